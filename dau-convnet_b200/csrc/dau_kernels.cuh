@@ -1,0 +1,101 @@
+// Device-side contracts shared by the DAU kernels and their host launchers.
+#pragma once
+#include "dau_common.hpp"
+
+#include <cstring>
+
+namespace dau {
+
+// ---- unit table -----------------------------------------------------------------------
+// One record per DAU unit and per use (forward / dL/dx / parameter gradients), 32 bytes so
+// a warp fetches it with two broadcast LDS.128.  A record describes a displaced 2x2-tap
+// gather:   out[y][x] (+)= sum_{dy,dx in {0,1}} wt[dy][dx] * in[y + offy + dy][x + offx + dx]
+// with (offx, offy) stored relative to the top-left corner of the haloed tile, i.e.
+// offx_h = offx + halo_x >= 0, offy_h = offy + halo_y >= 0.
+struct __align__(16) UnitRec {
+    float w00, w01, w10, w11;   // wt[dy][dx]
+    int offx_h, offy_h;         // integer displacement + halo
+    int pad0, pad1;
+};
+static_assert(sizeof(UnitRec) == 32, "UnitRec must be 32 bytes");
+
+enum UnitTableMode {
+    UNITS_FORWARD = 0,   // table[s][f][g]: off=floor(mu),    wt = w * bilinear(frac)
+    UNITS_BACKPROP = 1,  // table[f][s][g]: off=floor(-mu),   wt = w * bilinear(frac(-mu))
+    UNITS_GRADIENT = 2   // table[s][f][g]: off=-floor(mu)-1, wt = bilinear flipped, no w
+};
+
+struct UnitPrepArgs {
+    const float* w; const float* mu1; const float* mu2;   // [1,S,G,F]
+    int S, G, F;
+    int g_active;            // G - number_units_ignore
+    int halo_x, halo_y;      // halo_x is rounded up to the column-interleave factor
+    int max_off;             // kernel_size/2: integer offsets are clamped to [-max_off, max_off-1]
+    int use_interpolation;
+};
+
+void launch_unit_prep(const UnitPrepArgs& a, UnitRec* fwd, UnitRec* bwd, UnitRec* grad,
+                      int* nan_flag, cudaStream_t stream);
+
+// in-place parameter clipping (unit_bounds_guard, base_dau_conv_layer.cu:33-49)
+void launch_clip_params(float* mu1, float* mu2, float* sigma, int n, float mu_lo, float mu_hi,
+                        float sigma_lo, cudaStream_t stream);
+
+// ---- blur ------------------------------------------------------------------------------
+void launch_blur_single(const float* in, float* out, int planes, int H, int W, int kb,
+                        const float* fx, const float* fy, cudaStream_t stream);
+void launch_blur_bank(const float* in, float* out4, int planes, int H, int W,
+                      const BlurFactors& f, cudaStream_t stream);
+
+// ---- displaced gather (forward and dL/dx) -------------------------------------------------
+struct GatherPlan {            // chosen once per shape by plan_gather()
+    int variant;               // index into the instantiated tile shapes
+    int tile_w, tile_h, imgs;  // output tile of one CTA: imgs x tile_h x tile_w
+    int halo_x, halo_y;
+    int row_stride, img_stride;// shared-memory strides in words (bank-conflict padded)
+    int stage_words;           // words per pipeline stage (tile + unit records)
+    int cout_per_cta;
+    size_t smem_bytes;
+    int grid_x, grid_y, grid_z;
+};
+GatherPlan plan_gather(int N, int Cin, int Cout, int G, int H, int W, int max_off);
+// out[n,co,y,x] = sum_{ci,g} gather(in[n,ci], table[ci][co][g]) (+ bias[co])
+void launch_gather(const GatherPlan& p, const float* in, const UnitRec* table, const float* bias,
+                   float* out, int N, int Cin, int Cout, int G, int H, int W, cudaStream_t stream);
+
+// ---- parameter gradients -----------------------------------------------------------------
+struct GradPlan {
+    int variant;
+    int tile_w, tile_h, imgs;
+    int halo_x, halo_y;
+    int row_stride, feat_stride, img_stride;
+    int feats_per_cta;         // FC: features whose error tiles share one stage
+    int units_per_warp;        // FC * G  (<= 16)
+    int g_chunk;               // units of one (s,f) handled per pass (G or 16)
+    int n_splits;              // CTAs along the (image,tile) reduction axis
+    size_t smem_bytes;
+    int grid_x, grid_y, grid_z;
+    size_t partial_floats;     // n_splits * 4 * S*G*F
+};
+GradPlan plan_grad(int N, int S, int F, int G, int H, int W, int max_off, int num_sms);
+// partial[split][k][s][g][f] = sum over the split's (n,y,x) of  xk[n,s,k] * gather(err[n,f])
+void launch_grad(const GradPlan& p, const float* xk, const float* err, const UnitRec* table,
+                 float* partial, int N, int S, int F, int G, int H, int W,
+                 int mask_last_row, int mask_last_col, cudaStream_t stream);
+
+struct GradFinalizeArgs {
+    const float* partial; int n_splits;
+    const float* w;
+    float* dw; float* dmu1; float* dmu2; float* dsigma;   // any may be NULL
+    int S, G, F, g_active;
+    float mu_lr;
+};
+void launch_grad_finalize(const GradFinalizeArgs& a, cudaStream_t stream);
+
+// bias gradient: dbias[f] += sum_{n,y,x} err[n,f,y,x]
+void launch_bias_grad(const float* err, float* dbias, int N, int F, int HW, cudaStream_t stream);
+
+// FP32 FMA peak probe (register-resident FFMA chains on every SM)
+void launch_fma_probe(float* sink, int iters, int blocks, cudaStream_t stream);
+
+}  // namespace dau

@@ -1,0 +1,267 @@
+// Host orchestration of the B200 DAU layer (see dau_layer.hpp).  Follows the order of work of
+// BaseDAUConvLayer<T>::Forward_gpu / Backward_gpu (reference
+// src/dau_conv/base_dau_conv_layer.cu:16-127, 131-363) with the re-layout kernels, memsets,
+// side streams, cuBLAS calls and host syncs of the reference removed:
+//   forward : [clip] -> blur(X) -> unit table -> gather                         (3-4 launches)
+//   backward: blur bank(X) -> unit tables -> gradient kernel -> finalize
+//             blur(E, rotated) -> gather with the transposed table  [-> bias]   (6-7 launches)
+#include "dau_layer.hpp"
+
+#include <cmath>
+#include <cstring>
+
+namespace dau {
+
+namespace {
+size_t align_up(size_t v, size_t a = 256) { return (v + a - 1) / a * a; }
+
+// ignore_edge_gradients: zero the last error column/row when the extent is a multiple of the
+// reference's patch size (dau_conv_test.py:110-136, base_dau_conv_layer.cpp:763-771,
+// dau_conv_backward_core.hpp:2218-2222).
+bool edge_rule(int n) {
+    const int patches[4] = {64, 32, 16, 8};
+    for (int p : patches)
+        if (n >= p) return n % p == 0;
+    return false;
+}
+
+const char* kFwdNames[] = {"clip_params", "blur_input", "unit_table", "gather_forward"};
+const char* kBwdNames[] = {"blur_bank", "unit_tables", "grad_units", "grad_finalize",
+                           "blur_error", "gather_backprop", "bias_grad"};
+}  // namespace
+
+DAUConvLayerB200::DAUConvLayerB200(const dau_settings_t& s, int device) : st_(s), device_(device) {
+    // LayerSetUp checks (base_dau_conv_layer.cpp:29-187)
+    DAU_CHECK(s.num_output > 0, 1, "num_output must be positive");
+    DAU_CHECK(s.number_units_x > 0 && s.number_units_y > 0, 1, "number_units must be positive");
+    DAU_CHECK(s.stride == 1, 4, "DAUConvolution current supports only stride == 1");   // .cpp:68-69
+    DAU_CHECK(s.kernel_size >= 3 && (s.kernel_size & 1) == 1, 1, "kernel_size must be odd and >= 3");
+    DAU_CHECK(s.kernel_size / 2 <= 32, 4, "kernel_size above 65 is not supported (dau_conv_op.cpp:250-253)");
+    DAU_CHECK(s.pad == (s.kernel_size - 1) / 2, 4, "only pad == (kernel_size-1)/2 is supported (output size == input size)");
+    DAU_CHECK(s.offsets_already_centered != 0, 4, "only centred offsets are supported");
+    G_ = s.number_units_x * s.number_units_y;
+    DAU_CHECK(s.number_units_ignore >= 0 && s.number_units_ignore < G_ + 1, 1, "number_units_ignore out of range");
+    F_ = s.num_output;
+    max_off_ = s.kernel_size / 2;
+    DAU_CUDA_CHECK(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    DAU_CUDA_CHECK(cudaGetDeviceProperties(&prop, device));
+    DAU_CHECK(prop.major >= 10, 4, "this library is built for sm_100a (B200) only");
+    num_sms_ = prop.multiProcessorCount;
+}
+
+DAUConvLayerB200::~DAUConvLayerB200() {
+    for (int w = 0; w < 2; ++w)
+        for (auto& sl : slots_[w]) { cudaEventDestroy(sl.beg); cudaEventDestroy(sl.end); }
+}
+
+void DAUConvLayerB200::Reshape(int N, int S, int H, int W, size_t* fwd_ws, size_t* bwd_ws) {
+    DAU_CHECK(N > 0 && S > 0 && H > 0 && W > 0, 1, "bottom shape must be a positive 4-D NCHW shape");
+    N_ = N; S_ = S; H_ = H; W_ = W;
+    const size_t act_in = (size_t)N * S * H * W, act_out = (size_t)N * F_ * H * W;
+    const size_t units = (size_t)S * G_ * F_;
+    fwd_plan_ = plan_gather(N, S, F_, G_, H, W, max_off_);
+    bwd_plan_ = plan_gather(N, F_, S, G_, H, W, max_off_);
+    grad_plan_ = plan_grad(N, S, F_, G_, H, W, max_off_, num_sms_);
+    // forward workspace: blurred input | unit table | flag
+    size_t o = 0;
+    off_fwd_blur_ = o;  o = align_up(o + act_in * sizeof(float));
+    off_fwd_table_ = o; o = align_up(o + units * sizeof(UnitRec));
+    off_fwd_flag_ = o;  o = align_up(o + 256);
+    fwd_ws_ = o;
+    // backward workspace: 4 derivative blurs | blurred error | two unit tables | split partials | flag
+    o = 0;
+    off_bwd_xk_ = o;      o = align_up(o + 4 * act_in * sizeof(float));
+    off_bwd_eb_ = o;      o = align_up(o + act_out * sizeof(float));
+    off_bwd_table_ = o;   o = align_up(o + units * sizeof(UnitRec));
+    off_bwd_gtable_ = o;  o = align_up(o + units * sizeof(UnitRec));
+    off_bwd_partial_ = o; o = align_up(o + grad_plan_.partial_floats * sizeof(float));
+    off_bwd_flag_ = o;    o = align_up(o + 256);
+    bwd_ws_ = o;
+    shaped_ = true;
+    if (fwd_ws) *fwd_ws = fwd_ws_;
+    if (bwd_ws) *bwd_ws = bwd_ws_;
+}
+
+const BlurFactors& DAUConvLayerB200::factors_for(const float* sigma_dev, cudaStream_t stream) {
+    float sigma = sigma_hint_;
+    if (!(sigma > 0.f)) {
+        // the reference reads sigma[0] with a blocking copy in LayerSetUp
+        // (base_dau_conv_layer.hpp:266-275); same here unless a hint was given
+        DAU_CHECK(sigma_dev != nullptr, 1, "sigma pointer is NULL");
+        DAU_CUDA_CHECK(cudaMemcpyAsync(&sigma, sigma_dev, sizeof(float), cudaMemcpyDeviceToHost, stream));
+        DAU_CUDA_CHECK(cudaStreamSynchronize(stream));
+    }
+    DAU_CHECK(sigma > 0.f && std::isfinite(sigma), 1, "sigma must be a positive finite number");
+    if (sigma != cached_sigma_) {
+        FilterOptions opt;
+        opt.unit_normalization = st_.unit_normalization != 0;
+        opt.square_unit_normalization = st_.square_unit_normalization != 0;
+        opt.single_dimension_kernel = st_.single_dimension_kernel != 0;
+        opt.forbid_positive_dim1 = st_.forbid_positive_dim1 != 0;
+        compute_blur_factors(sigma, opt, &factors_);
+        cached_sigma_ = sigma;
+    }
+    return factors_;
+}
+
+void DAUConvLayerB200::enable_timing(bool e) {
+    timing_ = e;
+    if (e && slots_[0].empty()) {
+        for (int w = 0; w < 2; ++w) {
+            const int n = w == 0 ? 4 : 7;
+            for (int i = 0; i < n; ++i) {
+                TimingSlot sl; sl.name = w == 0 ? kFwdNames[i] : kBwdNames[i]; sl.used = false;
+                DAU_CUDA_CHECK(cudaEventCreate(&sl.beg));
+                DAU_CUDA_CHECK(cudaEventCreate(&sl.end));
+                slots_[w].push_back(sl);
+            }
+        }
+    }
+}
+
+const char* DAUConvLayerB200::timing_name(int which, int idx) {
+    if (which == 0 && idx >= 0 && idx < 4) return kFwdNames[idx];
+    if (which == 1 && idx >= 0 && idx < 7) return kBwdNames[idx];
+    return nullptr;
+}
+
+int DAUConvLayerB200::get_timing(int which, float* ms, int cap) {
+    if (which < 0 || which > 1 || slots_[which].empty()) return 0;
+    int n = 0;
+    for (auto& sl : slots_[which]) {
+        if (n >= cap) break;
+        float t = 0.f;
+        if (sl.used) { cudaEventSynchronize(sl.end); cudaEventElapsedTime(&t, sl.beg, sl.end); }
+        ms[n++] = t;
+    }
+    return n;
+}
+
+void DAUConvLayerB200::tic(int which, int idx, cudaStream_t s) {
+    ++launches_;
+    if (timing_) { slots_[which][idx].used = true; cudaEventRecord(slots_[which][idx].beg, s); }
+}
+void DAUConvLayerB200::toc(int which, int idx, cudaStream_t s) {
+    if (timing_) cudaEventRecord(slots_[which][idx].end, s);
+}
+
+void DAUConvLayerB200::Forward_gpu(const float* bottom, float* w, float* mu1, float* mu2, float* sigma,
+                                   const float* bias, float* top, void* ws, size_t ws_bytes,
+                                   cudaStream_t stream) {
+    DAU_CHECK(shaped_, 3, "Forward_gpu called before Reshape");
+    DAU_CHECK(bottom && w && mu1 && mu2 && top, 1, "NULL tensor pointer");
+    DAU_CHECK(ws != nullptr && ws_bytes >= fwd_ws_, 3, "forward workspace missing or too small");
+    DAU_CHECK(!st_.bias_term || bias, 1, "bias_term is set but bias pointer is NULL");
+    DAU_CUDA_CHECK(cudaSetDevice(device_));
+    if (timing_) for (auto& sl : slots_[0]) sl.used = false;
+    char* base = static_cast<char*>(ws);
+    float* xb = reinterpret_cast<float*>(base + off_fwd_blur_);
+    UnitRec* table = reinterpret_cast<UnitRec*>(base + off_fwd_table_);
+    int* flag = reinterpret_cast<int*>(base + off_fwd_flag_);
+    const int units = S_ * G_ * F_;
+
+    if (st_.unit_bounds_guard) {                      // base_dau_conv_layer.cu:33-49
+        tic(0, 0, stream);
+        const float lim = (float)max_off_ - st_.component_border_bound;
+        launch_clip_params(mu1, mu2, sigma, units, -lim, lim, st_.sigma_lower_bound, stream);
+        toc(0, 0, stream);
+    }
+    const BlurFactors& f = factors_for(sigma, stream);
+
+    tic(0, 1, stream);
+    launch_blur_single(bottom, xb, N_ * S_, H_, W_, f.kb, f.fwd_x, f.fwd_y, stream);
+    toc(0, 1, stream);
+
+    tic(0, 2, stream);
+    UnitPrepArgs ua;
+    ua.w = w; ua.mu1 = mu1; ua.mu2 = mu2; ua.S = S_; ua.G = G_; ua.F = F_;
+    ua.g_active = G_ - st_.number_units_ignore;
+    ua.halo_x = fwd_plan_.halo_x; ua.halo_y = fwd_plan_.halo_y; ua.max_off = max_off_;
+    ua.use_interpolation = st_.use_interpolation;
+    launch_unit_prep(ua, table, nullptr, nullptr, flag, stream);
+    toc(0, 2, stream);
+
+    tic(0, 3, stream);
+    launch_gather(fwd_plan_, xb, table, st_.bias_term ? bias : nullptr, top, N_, S_, F_, G_, H_, W_, stream);
+    toc(0, 3, stream);
+}
+
+void DAUConvLayerB200::Backward_gpu(const float* bottom, const float* top_error, const float* w,
+                                    const float* mu1, const float* mu2, const float* sigma,
+                                    float* bottom_error, float* dw, float* dmu1, float* dmu2,
+                                    float* dsigma, float* dbias, unsigned flags, void* ws,
+                                    size_t ws_bytes, cudaStream_t stream) {
+    DAU_CHECK(shaped_, 3, "Backward_gpu called before Reshape");
+    DAU_CHECK(bottom && top_error && w && mu1 && mu2, 1, "NULL tensor pointer");
+    DAU_CHECK(ws != nullptr && ws_bytes >= bwd_ws_, 3, "backward workspace missing or too small");
+    DAU_CUDA_CHECK(cudaSetDevice(device_));
+    if (timing_) for (auto& sl : slots_[1]) sl.used = false;
+    char* base = static_cast<char*>(ws);
+    float* xk = reinterpret_cast<float*>(base + off_bwd_xk_);
+    float* eb = reinterpret_cast<float*>(base + off_bwd_eb_);
+    UnitRec* btable = reinterpret_cast<UnitRec*>(base + off_bwd_table_);
+    UnitRec* gtable = reinterpret_cast<UnitRec*>(base + off_bwd_gtable_);
+    float* partial = reinterpret_cast<float*>(base + off_bwd_partial_);
+    int* flag = reinterpret_cast<int*>(base + off_bwd_flag_);
+    const BlurFactors& f = factors_for(sigma, stream);
+
+    const bool want_params = (flags & (DAU_GRAD_W | DAU_GRAD_MU1 | DAU_GRAD_MU2 | DAU_GRAD_SIGMA)) != 0;
+    const bool want_input = (flags & DAU_GRAD_INPUT) != 0;
+    if (want_input) DAU_CHECK(bottom_error != nullptr, 1, "bottom_error is NULL but DAU_GRAD_INPUT is set");
+
+    UnitPrepArgs ua;
+    ua.w = w; ua.mu1 = mu1; ua.mu2 = mu2; ua.S = S_; ua.G = G_; ua.F = F_;
+    ua.g_active = G_ - st_.number_units_ignore;
+    ua.max_off = max_off_; ua.use_interpolation = st_.use_interpolation;
+
+    if (want_params) {
+        tic(1, 0, stream);
+        launch_blur_bank(bottom, xk, N_ * S_, H_, W_, f, stream);
+        toc(1, 0, stream);
+    }
+    {
+        // both tables in one launch (their halos are the same by construction: same halo class)
+        tic(1, 1, stream);
+        ua.halo_x = grad_plan_.halo_x; ua.halo_y = grad_plan_.halo_y;
+        DAU_CHECK(bwd_plan_.halo_x == grad_plan_.halo_x && bwd_plan_.halo_y == grad_plan_.halo_y, 3,
+                  "internal: halo mismatch between back-propagation and gradient plans");
+        launch_unit_prep(ua, nullptr, want_input ? btable : nullptr, want_params ? gtable : nullptr, flag, stream);
+        toc(1, 1, stream);
+    }
+    if (want_params) {
+        tic(1, 2, stream);
+        const int mrow = st_.ignore_edge_gradients && edge_rule(H_) ? 1 : 0;
+        const int mcol = st_.ignore_edge_gradients && edge_rule(W_) ? 1 : 0;
+        launch_grad(grad_plan_, xk, top_error, gtable, partial, N_, S_, F_, G_, H_, W_, mrow, mcol, stream);
+        toc(1, 2, stream);
+        tic(1, 3, stream);
+        GradFinalizeArgs fa;
+        fa.partial = partial; fa.n_splits = grad_plan_.n_splits; fa.w = w;
+        fa.dw = (flags & DAU_GRAD_W) ? dw : nullptr;
+        fa.dmu1 = (flags & DAU_GRAD_MU1) ? dmu1 : nullptr;
+        fa.dmu2 = (flags & DAU_GRAD_MU2) ? dmu2 : nullptr;
+        fa.dsigma = ((flags & DAU_GRAD_SIGMA) && st_.learn_sigma) ? dsigma : nullptr;
+        fa.S = S_; fa.G = G_; fa.F = F_; fa.g_active = G_ - st_.number_units_ignore;
+        fa.mu_lr = st_.mu_learning_rate_factor;
+        launch_grad_finalize(fa, stream);
+        toc(1, 3, stream);
+    }
+    if (want_input) {
+        // blur the error with the rotated filter, then gather with -mu and the parameters read
+        // transposed (base_dau_conv_layer.cu:278-325)
+        tic(1, 4, stream);
+        launch_blur_single(top_error, eb, N_ * F_, H_, W_, f.kb, f.err_x, f.err_y, stream);
+        toc(1, 4, stream);
+        tic(1, 5, stream);
+        launch_gather(bwd_plan_, eb, btable, nullptr, bottom_error, N_, F_, S_, G_, H_, W_, stream);
+        toc(1, 5, stream);
+    }
+    if ((flags & DAU_GRAD_BIAS) && st_.bias_term && dbias) {
+        tic(1, 6, stream);
+        launch_bias_grad(top_error, dbias, N_, F_, H_ * W_, stream);
+        toc(1, 6, stream);
+    }
+}
+
+}  // namespace dau

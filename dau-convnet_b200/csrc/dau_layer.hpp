@@ -1,0 +1,73 @@
+// DAUConvLayerB200: host-side orchestration of the B200 DAU layer.
+//
+// Keeps the contract of BaseDAUConvLayer<float> (reference
+// include/dau_conv/base_dau_conv_layer.hpp:177-225): LayerSetUp -> Reshape -> Forward_gpu /
+// Backward_gpu, the enable_* / set_* toggles and "the caller owns every buffer"
+// (:229-264, :413-415).  The virtual buffer accessors of the reference (param_w(),
+// temp_interm_buffer(), allocate_workspace_mem() ...) become explicit pointer arguments plus
+// ONE caller-provided workspace whose size Reshape reports.
+#pragma once
+#include "dau_kernels.cuh"
+#include "../../include/dau_conv_b200.h"
+
+#include <string>
+#include <vector>
+
+namespace dau {
+
+struct TimingSlot { const char* name; cudaEvent_t beg, end; bool used; };
+
+class DAUConvLayerB200 {
+public:
+    DAUConvLayerB200(const dau_settings_t& settings, int device);
+    ~DAUConvLayerB200();
+
+    // (LayerSetUp happens in the constructor: settings validation, G, halo.)
+    void Reshape(int N, int S, int H, int W, size_t* fwd_ws, size_t* bwd_ws);
+
+    void Forward_gpu(const float* bottom, float* w, float* mu1, float* mu2, float* sigma,
+                     const float* bias, float* top, void* ws, size_t ws_bytes, cudaStream_t stream);
+
+    void Backward_gpu(const float* bottom, const float* top_error, const float* w, const float* mu1,
+                      const float* mu2, const float* sigma, float* bottom_error, float* dw,
+                      float* dmu1, float* dmu2, float* dsigma, float* dbias, unsigned flags,
+                      void* ws, size_t ws_bytes, cudaStream_t stream);
+
+    void set_sigma_hint(float v) { sigma_hint_ = v; }
+    void enable_timing(bool e);
+    int  get_timing(int which, float* ms, int cap);
+    static const char* timing_name(int which, int idx);
+    long long launches() const { return launches_; }
+
+    int N() const { return N_; } int S() const { return S_; } int F() const { return F_; }
+    int G() const { return G_; } int H() const { return H_; } int W() const { return W_; }
+    int device() const { return device_; }
+    const dau_settings_t& settings() const { return st_; }
+    const GatherPlan& fwd_plan() const { return fwd_plan_; }
+    const GradPlan& grad_plan() const { return grad_plan_; }
+
+private:
+    const BlurFactors& factors_for(const float* sigma_dev, cudaStream_t stream);
+    void tic(int which, int idx, cudaStream_t s);
+    void toc(int which, int idx, cudaStream_t s);
+
+    dau_settings_t st_;
+    int device_, num_sms_;
+    int N_ = 0, S_ = 0, H_ = 0, W_ = 0, F_ = 0, G_ = 0, max_off_ = 0;
+    bool shaped_ = false;
+    GatherPlan fwd_plan_{}, bwd_plan_{};
+    GradPlan grad_plan_{};
+    size_t fwd_ws_ = 0, bwd_ws_ = 0;
+    // workspace carving (byte offsets)
+    size_t off_fwd_blur_ = 0, off_fwd_table_ = 0, off_fwd_flag_ = 0;
+    size_t off_bwd_xk_ = 0, off_bwd_eb_ = 0, off_bwd_table_ = 0, off_bwd_gtable_ = 0,
+           off_bwd_partial_ = 0, off_bwd_flag_ = 0;
+    float sigma_hint_ = 0.f;
+    float cached_sigma_ = -1.f;
+    BlurFactors factors_{};
+    bool timing_ = false;
+    std::vector<TimingSlot> slots_[2];
+    long long launches_ = 0;
+};
+
+}  // namespace dau

@@ -1,0 +1,169 @@
+// Small O(S*G*F) kernels around the hot loops: unit-table preparation, parameter clipping,
+// gradient finalisation, bias gradient, and the FP32-FMA peak probe used by bench.py.
+//
+// Unit-table preparation replaces perpare_weights_and_offsets (forward,
+// include/dau_conv/dau_conv_impl/dau_conv_forward_core.hpp:1858-2215: floor(mu) -> offset
+// :2025-2028, frac(mu) -> 4 bilinear factors x w :2155-2213) and
+// perpare_weights_and_offsets_bw_multi (backward, dau_conv_backward_core.hpp:1824-2115:
+// bilinear factors WITHOUT w :2078-2081, moved onto the error :846-894), plus the
+// "negate mu for back-propagation" memcpy + cublasSscal (base_dau_conv_layer.cu:299-315).
+#include "dau_kernels.cuh"
+
+namespace dau {
+
+namespace {
+
+__device__ __forceinline__ void split_offset(float mu, int max_off, int use_interp, int& o, float& f) {
+    float fl = floorf(mu);
+    f = mu - fl;
+    if (fl < (float)(-max_off)) { fl = (float)(-max_off); f = 0.f; }
+    if (fl > (float)(max_off - 1)) { fl = (float)(max_off - 1); f = use_interp ? 1.f : 0.f; }
+    if (!use_interp) f = 0.f;      // taps = floor only (dau_conv_forward_core.hpp:2399-2400)
+    o = (int)fl;
+}
+
+__global__ void unit_prep_kernel(UnitPrepArgs a, UnitRec* __restrict__ fwd, UnitRec* __restrict__ bwd,
+                                 UnitRec* __restrict__ grad, int* __restrict__ nan_flag) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int total = a.S * a.G * a.F;
+    if (i >= total) return;
+    const int f = i % a.F, g = (i / a.F) % a.G, s = i / (a.F * a.G);
+    float w = a.w[i], m1 = a.mu1[i], m2 = a.mu2[i];
+    if (isnan(m1) || isnan(m2)) {           // reference: FAILED_PRECONDITION (dau_conv_op.cpp:258-262)
+        if (nan_flag) atomicExch(nan_flag, 1);
+        m1 = 0.f; m2 = 0.f; w = 0.f;
+    }
+    int ox, oy; float fx, fy;
+    split_offset(m1, a.max_off, a.use_interpolation, ox, fx);
+    split_offset(m2, a.max_off, a.use_interpolation, oy, fy);
+    const float b00 = (1.f - fx) * (1.f - fy), b01 = fx * (1.f - fy);
+    const float b10 = (1.f - fx) * fy, b11 = fx * fy;
+    if (fwd) {
+        const float wa = g < a.g_active ? w : 0.f;   // dummy units do not contribute (dau_conv_test.py:33)
+        UnitRec r;
+        r.w00 = wa * b00; r.w01 = wa * b01; r.w10 = wa * b10; r.w11 = wa * b11;
+        r.offx_h = ox + a.halo_x; r.offy_h = oy + a.halo_y; r.pad0 = 0; r.pad1 = 0;
+        fwd[((size_t)s * a.F + f) * a.G + g] = r;
+    }
+    if (grad) {
+        // gather of the ERROR around p' - o - 1 (see dau_grad.cu); tap order flips
+        UnitRec r;
+        r.w00 = b11; r.w01 = b10; r.w10 = b01; r.w11 = b00;
+        r.offx_h = -ox - 1 + a.halo_x; r.offy_h = -oy - 1 + a.halo_y; r.pad0 = 0; r.pad1 = 0;
+        grad[((size_t)s * a.F + f) * a.G + g] = r;
+    }
+    if (bwd) {
+        int bx, by; float gx, gy;
+        split_offset(-m1, a.max_off, a.use_interpolation, bx, gx);
+        split_offset(-m2, a.max_off, a.use_interpolation, by, gy);
+        UnitRec r;
+        r.w00 = w * (1.f - gx) * (1.f - gy); r.w01 = w * gx * (1.f - gy);
+        r.w10 = w * (1.f - gx) * gy;         r.w11 = w * gx * gy;
+        r.offx_h = bx + a.halo_x; r.offy_h = by + a.halo_y; r.pad0 = 0; r.pad1 = 0;
+        bwd[((size_t)f * a.S + s) * a.G + g] = r;
+    }
+}
+
+__global__ void clip_params_kernel(float* mu1, float* mu2, float* sigma, int n, float lo, float hi,
+                                   float sigma_lo) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    mu1[i] = fminf(fmaxf(mu1[i], lo), hi);
+    mu2[i] = fminf(fmaxf(mu2[i], lo), hi);
+    if (sigma) sigma[i] = fmaxf(sigma[i], sigma_lo);
+}
+
+// Sum the split partials, then the reference epilogue (base_dau_conv_layer.cu:330-356):
+// x w on mu1/mu2/sigma, accumulate into the caller's buffers, zero dummy units, NaN -> 0 on
+// the mu gradients; plus the TF grad op's mu_learning_rate_factor (dau_conv_grad_op.cpp:296-303).
+__global__ void grad_finalize_kernel(GradFinalizeArgs a) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int total = a.S * a.G * a.F;
+    if (i >= total) return;
+    const int g = (i / a.F) % a.G;
+    float r[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int sp = 0; sp < a.n_splits; ++sp) {
+        const float* p = a.partial + (size_t)sp * 4 * total;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) r[k] += p[(size_t)k * total + i];
+    }
+    const bool dead = g >= a.g_active;
+    const float w = a.w[i];
+    if (a.dw) a.dw[i] = dead ? 0.f : a.dw[i] + r[0];
+    if (a.dmu1) { float v = a.dmu1[i] + a.mu_lr * (r[1] * w); a.dmu1[i] = (dead || isnan(v)) ? 0.f : v; }
+    if (a.dmu2) { float v = a.dmu2[i] + a.mu_lr * (r[2] * w); a.dmu2[i] = (dead || isnan(v)) ? 0.f : v; }
+    if (a.dsigma) a.dsigma[i] = dead ? 0.f : a.dsigma[i] + r[3] * w;
+}
+
+// dbias[f] += sum_{n,hw} err[n,f,hw]   (reference: cublasSgemv with a ones vector,
+// base_dau_conv_layer.cpp:1116-1126).  One CTA per feature.
+__global__ void __launch_bounds__(256) bias_grad_kernel(const float* __restrict__ err, float* dbias,
+                                                       int N, int F, int HW) {
+    const int f = blockIdx.x;
+    float acc = 0.f;
+    for (int n = 0; n < N; ++n) {
+        const float* p = err + ((size_t)n * F + f) * HW;
+        for (int i = threadIdx.x; i < HW; i += 256) acc += p[i];
+    }
+    __shared__ float red[8];
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float t = 0.f;
+        for (int i = 0; i < 8; ++i) t += red[i];
+        dbias[f] += t;
+    }
+}
+
+// 8 independent FFMA chains per thread, register resident: measures the FP32 FMA pipe.
+__global__ void __launch_bounds__(256) fma_probe_kernel(float* sink, int iters) {
+    float a[8];
+    const float m = 1.0000001f, c = 1e-9f * (float)threadIdx.x;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a[j] = (float)(threadIdx.x + j);
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int rep = 0; rep < 8; ++rep) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) a[j] = fmaf(a[j], m, c);
+        }
+    }
+    float t = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) t += a[j];
+    if (t == 123.456f) sink[0] = t;    // never true; keeps the chains alive
+}
+
+}  // namespace
+
+void launch_unit_prep(const UnitPrepArgs& a, UnitRec* fwd, UnitRec* bwd, UnitRec* grad,
+                      int* nan_flag, cudaStream_t stream) {
+    const int total = a.S * a.G * a.F;
+    unit_prep_kernel<<<(total + 255) / 256, 256, 0, stream>>>(a, fwd, bwd, grad, nan_flag);
+    DAU_CUDA_CHECK(cudaGetLastError());
+}
+
+void launch_clip_params(float* mu1, float* mu2, float* sigma, int n, float mu_lo, float mu_hi,
+                        float sigma_lo, cudaStream_t stream) {
+    clip_params_kernel<<<(n + 255) / 256, 256, 0, stream>>>(mu1, mu2, sigma, n, mu_lo, mu_hi, sigma_lo);
+    DAU_CUDA_CHECK(cudaGetLastError());
+}
+
+void launch_grad_finalize(const GradFinalizeArgs& a, cudaStream_t stream) {
+    const int total = a.S * a.G * a.F;
+    grad_finalize_kernel<<<(total + 255) / 256, 256, 0, stream>>>(a);
+    DAU_CUDA_CHECK(cudaGetLastError());
+}
+
+void launch_bias_grad(const float* err, float* dbias, int N, int F, int HW, cudaStream_t stream) {
+    bias_grad_kernel<<<F, 256, 0, stream>>>(err, dbias, N, F, HW);
+    DAU_CUDA_CHECK(cudaGetLastError());
+}
+
+void launch_fma_probe(float* sink, int iters, int blocks, cudaStream_t stream) {
+    fma_probe_kernel<<<blocks, 256, 0, stream>>>(sink, iters);
+    DAU_CUDA_CHECK(cudaGetLastError());
+}
+
+}  // namespace dau

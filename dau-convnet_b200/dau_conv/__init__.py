@@ -1,0 +1,8 @@
+"""dau_conv: B200-native DAU convolution operator (drop-in for the reference's TF plugin package
+`dau_conv`, plugins/tensorflow/dau_conv/__init__.py)."""
+from . import _lib
+from ._lib import DAUError, default_settings, get_kernels
+from .functional import (DAULayerHandle, dau_conv, dau_conv_grad_op, dau_conv_op, get_handle)
+
+__all__ = ["DAUError", "default_settings", "get_kernels", "DAULayerHandle", "dau_conv",
+           "dau_conv_op", "dau_conv_grad_op", "get_handle"]

@@ -1,0 +1,209 @@
+"""The DAUConv / DAUConvGrad operators on top of the C ABI, with the TF op signatures.
+
+Mirrors (reference, plugins/tensorflow):
+  DAUConv(input, weights, mu1, mu2, sigma) -> output      src/dau_conv_op.cpp:22-84, 150-324
+  DAUConvGrad(grad, input, weights, mu1, mu2, sigma)
+      -> (grad_input, grad_weights, grad_mu1, grad_mu2, grad_sigma)   src/dau_conv_grad_op.cpp:18-49, 115-318
+  gradient registration                                   dau_conv/_dau_conv_grad_op.py:14-60
+
+torch is used for device memory and streams only; all arithmetic happens in
+libdau_conv_b200.so.  Tensors are NCHW fp32 on a CUDA device, parameters [1,S,G,F].
+"""
+import ctypes as C
+
+import torch
+
+from . import _lib
+
+# TF op attributes and their defaults (dau_conv_op.cpp:29-48)
+OP_ATTRS = dict(
+    number_units_x=2, number_units_y=2, number_units_ignore=0, num_output=64, kernel_size=9, pad=4,
+    stride=1, unit_normalization=True, square_unit_normalization=False, mean_iteration_step=1,
+    sigma_iteration_step=1, component_border_bound=1.0, sigma_lower_bound=0.3, merge_iteration_step=0,
+    merge_threshold=1, unit_testing=False, mu_learning_rate_factor=1.0, single_dim_kernel=False,
+    forbid_positive_dim1=False, use_interpolation=True,
+)
+
+
+def _settings_from_attrs(attrs):
+    a = dict(OP_ATTRS)
+    for k, v in attrs.items():
+        if k not in a:
+            raise TypeError("DAUConv: unknown attribute %r" % k)
+        a[k] = v
+    s = _lib.default_settings(
+        num_output=int(a["num_output"]), number_units_x=int(a["number_units_x"]),
+        number_units_y=int(a["number_units_y"]), number_units_ignore=int(a["number_units_ignore"]),
+        kernel_size=int(a["kernel_size"]), pad=int(a["pad"]), stride=int(a["stride"]),
+        unit_normalization=int(bool(a["unit_normalization"])),
+        square_unit_normalization=int(bool(a["square_unit_normalization"])),
+        mean_iteration_step=int(a["mean_iteration_step"]), sigma_iteration_step=int(a["sigma_iteration_step"]),
+        component_border_bound=float(a["component_border_bound"]), sigma_lower_bound=float(a["sigma_lower_bound"]),
+        merge_iteration_step=int(a["merge_iteration_step"]), merge_threshold=float(a["merge_threshold"]),
+        ignore_edge_gradients=int(bool(a["unit_testing"])),
+        mu_learning_rate_factor=float(a["mu_learning_rate_factor"]),
+        single_dimension_kernel=int(bool(a["single_dim_kernel"])),
+        forbid_positive_dim1=int(bool(a["forbid_positive_dim1"])),
+        use_interpolation=int(bool(a["use_interpolation"])),
+        unit_bounds_guard=0,           # the TF op disables the guard (dau_conv_op.cpp:283)
+        learn_sigma=1,                 # enable_sigma_learning(true) (dau_conv_grad_op.cpp:272)
+    )
+    return s, tuple(sorted(a.items()))
+
+
+class DAULayerHandle(object):
+    """One dau_handle_t (= one BaseDAUConvLayer object) with its caller-owned workspace."""
+
+    def __init__(self, settings, device):
+        self.settings = settings
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise RuntimeError("the DAU layer runs on CUDA devices only (no CPU fallback)")
+        self._h = C.c_void_p()
+        idx = self.device.index if self.device.index is not None else torch.cuda.current_device()
+        _lib.check(_lib.lib.dau_create(C.byref(settings), idx, C.byref(self._h)))
+        self._shape = None
+        self._ws = None
+        self.fwd_bytes = self.bwd_bytes = 0
+
+    def __del__(self):
+        try:
+            if self._h:
+                _lib.lib.dau_destroy(self._h)
+                self._h = C.c_void_p()
+        except Exception:
+            pass
+
+    def reshape(self, N, S, H, W):
+        if self._shape != (N, S, H, W):
+            f, b = C.c_size_t(0), C.c_size_t(0)
+            _lib.check(_lib.lib.dau_reshape(self._h, N, S, H, W, C.byref(f), C.byref(b)))
+            self.fwd_bytes, self.bwd_bytes = f.value, b.value
+            self._shape = (N, S, H, W)
+
+    def workspace(self, nbytes):
+        if self._ws is None or self._ws.numel() < nbytes:
+            self._ws = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
+        return self._ws
+
+    def set_sigma_hint(self, value):
+        _lib.check(_lib.lib.dau_set_sigma_hint(self._h, float(value)))
+
+    def enable_timing(self, enable=True):
+        _lib.check(_lib.lib.dau_enable_timing(self._h, int(enable)))
+
+    def timing(self, which):
+        buf = (C.c_float * 16)()
+        n = C.c_int(0)
+        _lib.check(_lib.lib.dau_get_timing(self._h, which, buf, 16, C.byref(n)))
+        return {_lib.lib.dau_timing_name(which, i).decode(): buf[i] for i in range(n.value)}
+
+    def launch_count(self):
+        return int(_lib.lib.dau_launch_count(self._h))
+
+    # -- the two calls of the contract ---------------------------------------------------------
+    def forward(self, x, w, mu1, mu2, sigma, bias=None, out=None):
+        N, S, H, W = x.shape
+        self.reshape(N, S, H, W)
+        F = self.settings.num_output
+        if out is None:
+            out = torch.empty((N, F, H, W), dtype=torch.float32, device=x.device)
+        ws = self.workspace(self.fwd_bytes)
+        stream = torch.cuda.current_stream(x.device).cuda_stream
+        _lib.check(_lib.lib.dau_forward(
+            self._h, x.data_ptr(), w.data_ptr(), mu1.data_ptr(), mu2.data_ptr(), sigma.data_ptr(),
+            bias.data_ptr() if bias is not None else None, out.data_ptr(),
+            ws.data_ptr(), ws.numel(), stream))
+        return out
+
+    def backward(self, x, top_error, w, mu1, mu2, sigma, flags=_lib.GRAD_ALL, grads=None, dbias=None):
+        """Returns (dx, dw, dmu1, dmu2, dsigma); param grads are accumulated into `grads` if given."""
+        N, S, H, W = x.shape
+        self.reshape(N, S, H, W)
+        dx = torch.empty_like(x) if flags & _lib.GRAD_INPUT else None
+        if grads is None:
+            grads = [torch.zeros_like(w) for _ in range(4)]     # the TF op pre-zeroes (grad_op.cpp:202-205)
+        ws = self.workspace(self.bwd_bytes)
+        stream = torch.cuda.current_stream(x.device).cuda_stream
+        _lib.check(_lib.lib.dau_backward(
+            self._h, x.data_ptr(), top_error.data_ptr(), w.data_ptr(), mu1.data_ptr(), mu2.data_ptr(),
+            sigma.data_ptr(), dx.data_ptr() if dx is not None else None,
+            grads[0].data_ptr(), grads[1].data_ptr(), grads[2].data_ptr(), grads[3].data_ptr(),
+            dbias.data_ptr() if dbias is not None else None, flags, ws.data_ptr(), ws.numel(), stream))
+        return (dx,) + tuple(grads)
+
+
+_HANDLES = {}
+
+
+def get_handle(device, **attrs):
+    settings, key = _settings_from_attrs(attrs)
+    dev = torch.device(device)
+    idx = dev.index if dev.index is not None else torch.cuda.current_device()
+    k = (key, idx)
+    h = _HANDLES.get(k)
+    if h is None:
+        h = DAULayerHandle(settings, torch.device("cuda", idx))
+        _HANDLES[k] = h
+    return h
+
+
+def _check_inputs(x, w, mu1, mu2, sigma, attrs):
+    for name, t in (("input", x), ("weights", w), ("mu1", mu1), ("mu2", mu2), ("sigma", sigma)):
+        if not t.is_cuda or t.dtype != torch.float32:
+            raise RuntimeError("DAUConv: %s must be a float32 CUDA tensor" % name)
+        if t.dim() != 4:
+            raise RuntimeError("DAUConv: %s must have rank 4" % name)      # dau_conv_op.cpp:49-84
+    num_output = attrs.get("num_output", OP_ATTRS["num_output"])
+    G = attrs.get("number_units_x", 2) * attrs.get("number_units_y", 2)
+    want = (1, x.shape[1], G, num_output)
+    for name, t in (("weights", w), ("mu1", mu1), ("mu2", mu2), ("sigma", sigma)):
+        if tuple(t.shape) != want:
+            raise RuntimeError("DAUConv: %s has shape %s, expected %s" % (name, tuple(t.shape), want))
+
+
+def dau_conv_op(input, weights, mu1, mu2, sigma, **attrs):
+    """TF op DAUConv: output[N,F,H,W] (forward only, no autograd)."""
+    _check_inputs(input, weights, mu1, mu2, sigma, attrs)
+    h = get_handle(input.device, **attrs)
+    return h.forward(input.contiguous(), weights.contiguous(), mu1.contiguous(), mu2.contiguous(),
+                     sigma.contiguous())
+
+
+def dau_conv_grad_op(grad, input, weights, mu1, mu2, sigma, **attrs):
+    """TF op DAUConvGrad: (grad_input, grad_weights, grad_mu1, grad_mu2, grad_sigma)."""
+    _check_inputs(input, weights, mu1, mu2, sigma, attrs)
+    h = get_handle(input.device, **attrs)
+    return h.backward(input.contiguous(), grad.contiguous(), weights.contiguous(), mu1.contiguous(),
+                      mu2.contiguous(), sigma.contiguous())
+
+
+class _DAUConvFunction(torch.autograd.Function):
+    """@ops.RegisterGradient("DAUConv") equivalent (_dau_conv_grad_op.py:14-60)."""
+
+    @staticmethod
+    def forward(ctx, input, weights, mu1, mu2, sigma, attrs):
+        ctx.attrs = attrs
+        ctx.save_for_backward(input, weights, mu1, mu2, sigma)
+        return dau_conv_op(input, weights, mu1, mu2, sigma, **attrs)
+
+    @staticmethod
+    def backward(ctx, grad):
+        input, weights, mu1, mu2, sigma = ctx.saved_tensors
+        flags = 0
+        need = ctx.needs_input_grad
+        if need[0]:
+            flags |= _lib.GRAD_INPUT
+        if any(need[1:5]):
+            flags |= _lib.GRAD_W | _lib.GRAD_MU1 | _lib.GRAD_MU2 | _lib.GRAD_SIGMA
+        _check_inputs(input, weights, mu1, mu2, sigma, ctx.attrs)
+        h = get_handle(input.device, **ctx.attrs)
+        dx, dw, dm1, dm2, dsg = h.backward(input.contiguous(), grad.contiguous(), weights.contiguous(),
+                                           mu1.contiguous(), mu2.contiguous(), sigma.contiguous(), flags=flags)
+        return (dx if need[0] else None, dw if need[1] else None, dm1 if need[2] else None,
+                dm2 if need[3] else None, dsg if need[4] else None, None)
+
+
+def dau_conv(input, weights, mu1, mu2, sigma, **attrs):
+    """Differentiable DAUConv (forward + registered gradient)."""
+    return _DAUConvFunction.apply(input, weights, mu1, mu2, sigma, attrs)

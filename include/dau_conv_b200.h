@@ -1,0 +1,144 @@
+/*
+ * dau_conv_b200.h -- C ABI of the B200-native DAU convolution layer.
+ *
+ * This is the drop-in boundary for the ONE hot path of skokec/DAU-ConvNet:
+ * BaseDAUConvLayer<float>::Forward_gpu / Backward_gpu and the TensorFlow ops
+ * DAUConv / DAUConvGrad built on top of them.  Plain pointers and sizes only; every
+ * pointer named *_dev is DEVICE memory owned by the caller, every call is ordered on
+ * the caller's CUDA stream (passed as void*; NULL = legacy default stream), nothing is
+ * allocated behind the caller's back except a few KB of per-handle constant tables.
+ *
+ * Reference interfaces replaced (paths relative to the reference checkout):
+ *   dau_settings_t      <- DAUConvSettings                   include/dau_conv/base_dau_conv_layer.hpp:109-130
+ *                          + ctor flags / toggles            include/dau_conv/base_dau_conv_layer.hpp:177-184, 208-225
+ *                          + TF op attrs                     plugins/tensorflow/src/dau_conv_op.cpp:29-48
+ *   dau_create          <- BaseDAUConvLayer ctor+LayerSetUp  src/dau_conv/base_dau_conv_layer.cpp:29-187
+ *   dau_reshape         <- Reshape / workspace sizing        src/dau_conv/base_dau_conv_layer.cpp:190-394
+ *   dau_forward         <- Forward_gpu                       src/dau_conv/base_dau_conv_layer.cu:16-127
+ *   dau_backward        <- Backward_gpu (+ TF grad scaling)  src/dau_conv/base_dau_conv_layer.cu:131-363,
+ *                                                            plugins/tensorflow/src/dau_conv_grad_op.cpp:296-303
+ *   dau_get_kernels     <- BaseDAUKernelCompute::get_kernels src/dau_conv/base_dau_conv_layer.cu:537-710
+ *   dau_status_t/_last_error <- DAUException                 include/dau_conv/util/common.hpp:38-64, 102-106
+ *
+ * Layouts are the reference's: activations NCHW fp32, parameters [1,S,G,F] fp32 with F
+ * fastest (base_dau_conv_layer.hpp:233); mu1 is the x (width) offset, mu2 the y (height)
+ * offset (base_dau_conv_layer.cpp:574-578).
+ */
+#ifndef DAU_CONV_B200_H_
+#define DAU_CONV_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DAU_B200_ABI_VERSION 1
+
+typedef enum dau_status_t {
+    DAU_OK = 0,
+    DAU_ERR_INVALID_ARGUMENT = 1, /* bad shape / setting (reference: DAU_CHECK failure) */
+    DAU_ERR_CUDA = 2,             /* a CUDA call or launch failed (reference: CUDA_CHECK) */
+    DAU_ERR_NOT_READY = 3,        /* forward/backward before reshape, workspace too small */
+    DAU_ERR_UNSUPPORTED = 4,      /* e.g. stride != 1, |mu| bucket > 32 (dau_conv_op.cpp:250-253) */
+    DAU_ERR_NAN_OFFSET = 5        /* NaN in mu1/mu2 (dau_conv_op.cpp:258-262, FAILED_PRECONDITION) */
+} dau_status_t;
+
+/* Mirrors DAUConvSettings + the layer toggles.  Zero-initialise, then dau_settings_default(). */
+typedef struct dau_settings_t {
+    int32_t num_output;            /* F */
+    int32_t number_units_x;        /* G = x*y (DAUConvSettings::number_units) */
+    int32_t number_units_y;
+    int32_t number_units_ignore;   /* trailing dummy units whose gradients are zeroed */
+    int32_t kernel_size;           /* max_kernel_size: |mu| < kernel_size/2; halo of the gather */
+    int32_t pad;                   /* only pad == (kernel_size-1)/2 (TF op, dau_conv_op.cpp:256) */
+    int32_t stride;                /* must be 1 (base_dau_conv_layer.cpp:68-69) */
+    int32_t bias_term;             /* 0/1: adds bias[F] in forward, reduces dbias in backward */
+    int32_t unit_normalization;    /* default 1 */
+    int32_t square_unit_normalization;
+    int32_t use_interpolation;     /* default 1; 0 = nearest-lower tap only */
+    int32_t single_dimension_kernel; /* DAUConv1d: only the centre row of the blur survives */
+    int32_t forbid_positive_dim1;
+    int32_t ignore_edge_gradients; /* TF attr unit_testing */
+    int32_t unit_bounds_guard;     /* clip mu/sigma IN PLACE before use (Forward_gpu :33-49) */
+    int32_t offsets_already_centered; /* must be 1 */
+    int32_t learn_sigma;           /* 0 => sigma gradient skipped (last_k_optional) */
+    float   component_border_bound;
+    float   sigma_lower_bound;
+    float   mu_learning_rate_factor; /* applied to dmu1,dmu2 by dau_backward (TF grad op) */
+    /* parsed-but-unused reference fields, accepted for signature parity */
+    int32_t mean_iteration_step, sigma_iteration_step, merge_iteration_step;
+    float   merge_threshold;
+} dau_settings_t;
+
+typedef struct dau_handle_s dau_handle_t;
+
+/* flags for dau_backward: which gradients to produce (params_propagate_down + propagate_down) */
+enum {
+    DAU_GRAD_INPUT = 1, DAU_GRAD_W = 2, DAU_GRAD_MU1 = 4, DAU_GRAD_MU2 = 8,
+    DAU_GRAD_SIGMA = 16, DAU_GRAD_BIAS = 32, DAU_GRAD_ALL = 31
+};
+
+const char* dau_last_error(void);          /* thread-local message of the last failure */
+int         dau_abi_version(void);
+void        dau_settings_default(dau_settings_t* s);
+
+dau_status_t dau_create(const dau_settings_t* settings, int device, dau_handle_t** out);
+void         dau_destroy(dau_handle_t* h);
+
+/* Shape-dependent setup.  Output shape is [N, F, H, W].  Reports the workspace the caller
+ * must lend to forward and backward (bytes, 256-byte aligned pointer expected). */
+dau_status_t dau_reshape(dau_handle_t* h, int N, int S, int H, int W,
+                         size_t* fwd_workspace_bytes, size_t* bwd_workspace_bytes);
+
+/* Optional: tell the layer sigma's value so that forward/backward need no 4-byte D2H read
+ * of sigma_dev[0] (the reference reads it every LayerSetUp, base_dau_conv_layer.hpp:266-275).
+ * value <= 0 re-enables the read. */
+dau_status_t dau_set_sigma_hint(dau_handle_t* h, float value);
+
+/* top[N,F,H,W] = DAU(bottom[N,S,H,W]); top is overwritten. bias_dev may be NULL. */
+dau_status_t dau_forward(dau_handle_t* h, const float* bottom_dev,
+                         float* w_dev, float* mu1_dev, float* mu2_dev, float* sigma_dev,
+                         const float* bias_dev, float* top_dev,
+                         void* workspace_dev, size_t workspace_bytes, void* stream);
+
+/* bottom_error[N,S,H,W] is overwritten; d{w,mu1,mu2,sigma}[1,S,G,F] (and dbias[F]) are
+ * ACCUMULATED INTO (caller pre-zeroes, dau_conv_grad_op.cpp:202-205).  dmu1/dmu2/dsigma
+ * carry the xw factor, dmu1/dmu2 also mu_learning_rate_factor, NaNs in dmu are zeroed. */
+dau_status_t dau_backward(dau_handle_t* h, const float* bottom_dev, const float* top_error_dev,
+                          const float* w_dev, const float* mu1_dev, const float* mu2_dev,
+                          const float* sigma_dev, float* bottom_error_dev,
+                          float* dw_dev, float* dmu1_dev, float* dmu2_dev, float* dsigma_dev,
+                          float* dbias_dev, unsigned flags,
+                          void* workspace_dev, size_t workspace_bytes, void* stream);
+
+/* DAUKernelCompute for one unit (w=1, mu=0): six Kb x Kb HOST arrays, row-major, axis 0 = y.
+ * Order: blur, d_w, d_mu1, d_mu2, d_sigma, d_error.  *kb_out = 2*ceil(5*sigma)+1. */
+dau_status_t dau_get_kernels(const dau_settings_t* settings, float sigma, int* kb_out,
+                             float* out6_host, size_t out_capacity_floats);
+
+/* Host-buffer convenience (what a non-CUDA host binds): copies H2D, runs, copies back. */
+dau_status_t dau_forward_host(dau_handle_t* h, int N, int S, int H, int W, const float* bottom,
+                              const float* w, const float* mu1, const float* mu2, const float* sigma,
+                              const float* bias, float* top);
+dau_status_t dau_backward_host(dau_handle_t* h, int N, int S, int H, int W, const float* bottom,
+                               const float* top_error, const float* w, const float* mu1,
+                               const float* mu2, const float* sigma, float* bottom_error,
+                               float* dw, float* dmu1, float* dmu2, float* dsigma, float* dbias,
+                               unsigned flags);
+
+/* Measurement helpers used by bench.py (not part of the reference contract). */
+dau_status_t dau_measure_fma_peak(int device, int iters, double* tflops_out, double* ms_out);
+/* Per-kernel device times (ms) of the last forward / backward on this handle, measured with
+ * CUDA events on the caller's stream when profiling is enabled. names: see dau_layer.cpp. */
+dau_status_t dau_enable_timing(dau_handle_t* h, int enable);
+dau_status_t dau_get_timing(dau_handle_t* h, int which, float* ms_out, int capacity, int* count_out);
+const char*  dau_timing_name(int which, int index);
+/* number of kernels launched by this handle since creation (for bench.py's gpu_launches) */
+long long    dau_launch_count(const dau_handle_t* h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DAU_CONV_B200_H_ */

@@ -1,0 +1,177 @@
+"""Parity of the CUDA path (through the C ABI) against the oracle and the golden fixtures.
+
+Tolerance (BASELINE.json north_star): 1e-4 relative / 1e-5 absolute in fp32 for the output
+and all five gradients.  For gradients, which are fp32 sums of up to N*H*W terms, the absolute
+term is scaled by max(1, max|ref|) of the tensor (documented in DESIGN.md).
+"""
+import ast
+import glob
+import os
+
+import numpy as np
+import pytest
+
+from oracle import dau_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+GOLDEN = sorted(p for p in glob.glob(os.path.join(HERE, "golden", "*.npz"))
+                if not os.path.basename(p).startswith("filters_"))
+RTOL, ATOL = 1e-4, 1e-5
+
+
+def close(got, ref, name, scale_atol=False):
+    got = np.asarray(got, np.float64)
+    ref = np.asarray(ref, np.float64)
+    assert got.shape == ref.shape, name
+    atol = ATOL * (max(1.0, float(np.abs(ref).max())) if scale_atol else 1.0)
+    err = np.abs(got - ref)
+    bad = err > atol + RTOL * np.abs(ref)
+    assert not bad.any(), "%s: %d/%d outside tolerance, max abs err %.3e (max|ref| %.3e)" % (
+        name, int(bad.sum()), bad.size, float(err.max()), float(np.abs(ref).max()))
+
+
+def run_layer(x, err, w, mu1, mu2, sigma, ks, **attrs):
+    import torch
+    import dau_conv
+    dev = torch.device("cuda:0")
+    S, G, F = w.shape[1:]
+    sig = np.full(w.shape, sigma, np.float32)
+    t = [torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32)).to(dev) for a in (x, w, mu1, mu2, sig)]
+    a = dict(num_output=F, number_units_x=1, number_units_y=G, kernel_size=ks, pad=(ks - 1) // 2)
+    a.update(attrs)
+    y = dau_conv.dau_conv_op(*t, **a)
+    g = dau_conv.dau_conv_grad_op(torch.from_numpy(np.ascontiguousarray(err, dtype=np.float32)).to(dev), *t, **a)
+    torch.cuda.synchronize()
+    return y.cpu().numpy(), [v.cpu().numpy() for v in g]
+
+
+@pytest.mark.parametrize("path", GOLDEN, ids=[os.path.basename(p)[:-4] for p in GOLDEN])
+def test_golden_fixture(path):
+    """Outputs of the reference's own DAUConvPython (tests/golden, oracle/make_golden.py)."""
+    d = np.load(path)
+    kw = ast.literal_eval(str(d["kwargs"]))
+    m = max(float(np.abs(d["mu1"]).max()), float(np.abs(d["mu2"]).max()))
+    ks = 9 if m < 4 else 17
+    attrs = dict(use_interpolation=kw.get("use_interpolation", True),
+                 number_units_ignore=kw.get("num_dau_units_ignore", 0),
+                 unit_testing=kw.get("unit_testing", True),
+                 single_dim_kernel=kw.get("single_dim_kernel", False),
+                 forbid_positive_dim1=kw.get("aggr_forbid_positive", False))
+    y, g = run_layer(d["x"], d["err"], d["w"], d["mu1"], d["mu2"], float(d["sigma"]), ks, **attrs)
+    close(y, d["y"], "y")
+    for got, name in zip(g, ("dx", "dw", "dmu1", "dmu2", "dsigma")):
+        close(got, d[name], name, scale_atol=name != "dx")
+
+
+# (N, W, H, S, F, units, max_kernel, mu_range): the reference's Quick matrix
+# (dau_conv_test.py:418-437) plus shapes that exercise partial tiles and odd channel counts
+SHAPES = [
+    (2, 65, 8, 33, 32, (1, 2), 9, 3), (1, 65, 8, 32, 32, (1, 2), 9, 3),
+    (1, 8, 8, 32, 32, (1, 2), 9, 3), (4, 8, 8, 32, 32, (1, 2), 9, 3),
+    (16, 32, 32, 32, 32, (2, 2), 9, 3), (16, 32, 32, 32, 32, (2, 2), 17, 6),
+    (16, 32, 32, 32, 32, (2, 2), 17, 3), (16, 32, 32, 3, 32, (2, 2), 17, 3),
+    (4, 64, 64, 3, 32, (2, 2), 33, 10),
+    (3, 27, 27, 8, 16, (1, 2), 9, 3), (5, 13, 13, 16, 8, (1, 2), 9, 3),
+    (2, 30, 21, 5, 7, (1, 3), 9, 3.9), (2, 6, 6, 16, 24, (2, 1), 17, 8),
+    (1, 40, 40, 2, 3, (1, 1), 65, 20), (2, 17, 70, 4, 9, (3, 3), 9, 2),
+    (2, 20, 20, 2, 2, (3, 6), 9, 3),
+]
+
+
+def _case(shape, seed):
+    N, W, H, S, F, units, ks, m = shape
+    G = units[0] * units[1]
+    rng = np.random.default_rng(seed)
+    x = rng.random((N, S, H, W)).astype(np.float32)
+    err = rng.standard_normal((N, F, H, W)).astype(np.float32)
+    w = (0.1 * rng.standard_normal((1, S, G, F))).astype(np.float32)
+    lim = ks // 2 - 0.01
+    mu1 = np.clip(rng.uniform(-m, m, (1, S, G, F)), -lim, lim).astype(np.float32)
+    mu2 = np.clip(rng.uniform(-m, m, (1, S, G, F)), -lim, lim).astype(np.float32)
+    return x, err, w, mu1, mu2, ks
+
+
+@pytest.mark.parametrize("shape", SHAPES, ids=["x".join(str(v) for v in s[:5]) + "_k%d" % s[6] for s in SHAPES])
+@pytest.mark.parametrize("edge", [True, False], ids=["edgemask", "exact"])
+def test_oracle_parity(shape, edge):
+    x, err, w, mu1, mu2, ks = _case(shape, 1234 + len(str(shape)))
+    y, g = run_layer(x, err, w, mu1, mu2, 0.5, ks, unit_testing=edge)
+    close(y, O.forward(x, w, mu1, mu2, [0.5]), "y")
+    ref = O.backward(x, err, w, mu1, mu2, [0.5], ignore_edge_gradients=edge)
+    for got, r, name in zip(g, ref, ("dx", "dw", "dmu1", "dmu2", "dsigma")):
+        close(got, r, name, scale_atol=name != "dx")
+
+
+def test_integer_offsets_are_pure_shifts_and_exact_at_borders():
+    """mu integer => bilinear weights are exactly {1,0,0,0}: output = shifted blur, zero fill."""
+    rng = np.random.default_rng(3)
+    x = rng.random((2, 2, 19, 23)).astype(np.float32)
+    w = np.ones((1, 2, 1, 3), np.float32)
+    mu1 = np.zeros_like(w); mu2 = np.zeros_like(w)
+    mu1[0, :, 0, 0], mu2[0, :, 0, 0] = 3, -2
+    mu1[0, :, 0, 1], mu2[0, :, 0, 1] = -4, 3
+    err = np.zeros((2, 3, 19, 23), np.float32)
+    y, _ = run_layer(x, err, w, mu1, mu2, 0.5, 9)
+    blur = O.correlate_same(x, O.get_filters(0.5)[0]).sum(1)
+    exp = np.zeros_like(y, dtype=np.float64)
+    exp[:, 0, 2:, :20] = blur[:, :17, 3:]
+    exp[:, 1, :16, 4:] = blur[:, 3:, :19]
+    exp[:, 2] = blur
+    close(y, exp, "shifted")
+    assert np.all(y[:, 0, :2, :] == 0) and np.all(y[:, 0, :, 20:] == 0)      # bit-exact zero fill
+    assert np.all(y[:, 1, 16:, :] == 0) and np.all(y[:, 1, :, :4] == 0)
+
+
+def test_mu_learning_rate_factor_and_accumulation():
+    import torch
+    import dau_conv
+    x, err, w, mu1, mu2, ks = _case((2, 16, 16, 4, 8, (1, 2), 9, 3), 99)
+    _, g1 = run_layer(x, err, w, mu1, mu2, 0.5, ks)
+    _, g2 = run_layer(x, err, w, mu1, mu2, 0.5, ks, mu_learning_rate_factor=500.0)
+    np.testing.assert_allclose(g2[2], 500.0 * g1[2], rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(g2[3], 500.0 * g1[3], rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(g2[1], g1[1], rtol=0, atol=0)
+    # backward ACCUMULATES into the parameter-gradient buffers (base_dau_conv_layer.cu:340-343)
+    dev = torch.device("cuda:0")
+    sig = np.full(w.shape, 0.5, np.float32)
+    t = [torch.from_numpy(a).to(dev) for a in (x, err, w, mu1, mu2, sig)]
+    h = dau_conv.get_handle(dev, num_output=8, number_units_x=1, number_units_y=2)
+    grads = [torch.full_like(t[2], 2.0) for _ in range(4)]
+    h.backward(t[0], t[1], t[2], t[3], t[4], t[5], grads=grads)
+    torch.cuda.synchronize()
+    np.testing.assert_allclose(grads[0].cpu().numpy(), g1[1] + 2.0, rtol=1e-6, atol=1e-6)
+
+
+def test_full_size_properties_config_c2():
+    """BASELINE config C2 (N=128, S=F=128, 64x64, G=4): size-independent identities.
+    (a) sum(E*Y) == sum_units w*dL/dw  (Y is linear in w; a checksum of all 3.4e10 unit-pixels)
+    (b) w=1, mu=0  =>  Y[:, f] == G * blur(sum_s X_s) for every f."""
+    import torch
+    import dau_conv
+    dev = torch.device("cuda:0")
+    N, S, F, G, H, W = 128, 128, 128, 4, 64, 64
+    gen = torch.Generator(device=dev); gen.manual_seed(5)
+    x = torch.rand((N, S, H, W), device=dev, generator=gen)
+    e = torch.randn((N, F, H, W), device=dev, generator=gen)
+    w = 0.1 * torch.randn((1, S, G, F), device=dev, generator=gen)
+    mu1 = (torch.rand((1, S, G, F), device=dev, generator=gen) * 8 - 4).clamp(-3.99, 3.99)
+    mu2 = (torch.rand((1, S, G, F), device=dev, generator=gen) * 8 - 4).clamp(-3.99, 3.99)
+    sg = torch.full((1, S, G, F), 0.5, device=dev)
+    a = dict(num_output=F, number_units_x=2, number_units_y=2, kernel_size=9, pad=4)
+    y = dau_conv.dau_conv_op(x, w, mu1, mu2, sg, **a)
+    dx, dw, dm1, dm2, ds = dau_conv.dau_conv_grad_op(e, x, w, mu1, mu2, sg, **a)
+    lhs = float((y.double() * e.double()).sum())
+    rhs = float((w.double() * dw.double()).sum())
+    scale = float((w.double() * dw.double()).abs().sum())
+    assert abs(lhs - rhs) <= 1e-4 * abs(rhs) + 1e-6 * scale, (lhs, rhs, scale)
+    for t in (dx, dm1, dm2, ds):
+        assert bool(torch.isfinite(t).all())
+    # (b)
+    ones = torch.ones_like(w); zeros = torch.zeros_like(w)
+    y1 = dau_conv.dau_conv_op(x, ones, zeros, zeros, sg, **a)
+    k = torch.from_numpy(O.get_filters(0.5)[0].astype(np.float32)).to(dev)[None, None]
+    ref = G * torch.nn.functional.conv2d(x.sum(1, keepdim=True), k, padding=3)
+    assert float((y1[:, :1] - ref).abs().max()) <= 1e-4 * float(ref.abs().max())
+    assert float((y1 - y1[:, :1]).abs().max()) == 0.0     # every feature saw the same units
