@@ -35,8 +35,9 @@ __all__ = [
 
 
 def blur_kernel_size(sigma: float) -> int:
-    """Kb = 2*ceil(5*sigma)+1  (base_dau_conv_layer.cpp:146-147)."""
-    return 2 * int(math.ceil(5.0 * float(sigma))) + 1
+    """Kb = 2*ceil(5*sigma)+1 with the product in fp32, as the reference's Dtype=float
+    arithmetic takes it (base_dau_conv_layer.cpp:146-147): 5*0.8f == 4.0f -> Kb = 9."""
+    return 2 * int(math.ceil(float(np.float32(5.0) * np.float32(sigma)))) + 1
 
 
 def get_filters(sigma, kb=None, unit_normalization=True, square_unit_normalization=False,
