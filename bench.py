@@ -1,0 +1,338 @@
+#!/usr/bin/env python3
+"""bench.py -- DAU conv fwd+bwd images/sec/layer on B200 (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--config c2|c1|c4|l2..l5]
+
+One "step" = dau_forward + dau_backward (all five gradients, sigma learned) of ONE DAU layer on
+one batch of synthetic NCHW fp32 input, through the C ABI of libdau_conv_b200.so.  The default
+workload is BASELINE.json configs[1] ("C2": N=128 per GPU, S=F=128, 64x64, G=4, sigma=0.5,
+|mu|<4).  With N>1 GPUs (launched by torchrun, one rank per GPU) the batch dimension is sharded:
+every rank runs the same per-GPU batch (weak scaling) and the [4,S,G,F] parameter gradients are
+all-reduced with NCCL inside the step; activations never cross GPUs.
+
+`--impl reference` times the CPU restatement of the reference's own CPU path (oracle/dau_cpu.c,
+all host threads) on a bounded sample of the same workload; rank 0 only.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "dau-convnet_b200"))
+
+METRIC = "dau_conv_fwd_bwd_images_per_sec_per_layer"
+UNIT = "images/s"
+
+# name: (N per GPU, S, F, G(units x, y), H, W, kernel_size, mu range)
+CONFIGS = {
+    "c1": (16, 32, 32, (1, 2), 32, 32, 9, 3.0),
+    "c2": (128, 128, 128, (2, 2), 64, 64, 9, 4.0),
+    "c4": (256, 512, 512, (1, 2), 28, 28, 17, 8.0),
+    # AlexNet-DAU default DAU layers (assumption A1 in BASELINE.md), per-GPU batch 256
+    "l2": (256, 96, 256, (1, 2), 27, 27, 9, 3.0),
+    "l3": (256, 256, 384, (1, 2), 13, 13, 9, 3.0),
+    "l4": (256, 384, 384, (1, 2), 13, 13, 9, 3.0),
+    "l5": (256, 384, 256, (1, 2), 13, 13, 9, 3.0),
+}
+
+
+def workload_name(cfg):
+    N, S, F, units, H, W, ks, m = CONFIGS[cfg]
+    return "%s: single DAU layer N=%d/GPU, S=%d, F=%d, %dx%d, G=%d, sigma=0.5, kernel_size=%d, |mu|<%g" % (
+        cfg.upper(), N, S, F, H, W, units[0] * units[1], ks, m)
+
+
+def make_inputs_numpy(cfg, n_images, seed):
+    import numpy as np
+    N, S, F, units, H, W, ks, m = CONFIGS[cfg]
+    G = units[0] * units[1]
+    rng = np.random.default_rng(seed)
+    lim = ks // 2 - 0.01
+    x = rng.random((n_images, S, H, W), dtype=np.float32)
+    e = rng.standard_normal((n_images, F, H, W), dtype=np.float32)
+    w = (0.1 * rng.standard_normal((1, S, G, F))).astype(np.float32)
+    mu1 = np.clip(rng.uniform(-m, m, (1, S, G, F)), -lim, lim).astype(np.float32)
+    mu2 = np.clip(rng.uniform(-m, m, (1, S, G, F)), -lim, lim).astype(np.float32)
+    return x, e, w, mu1, mu2
+
+
+class ClockSampler(threading.Thread):
+    """Samples nvidia-smi clocks / throttle reasons of one GPU while the timed region runs."""
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.proc = index, [], None
+
+    def run(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.FIELDS,
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            for line in self.proc.stdout:
+                self.rows.append([c.strip() for c in line.split(",")])
+        except Exception:
+            pass
+
+    def stop(self):
+        if self.proc is not None:
+            self.proc.terminate()
+        self.join(timeout=2)
+
+    def summary(self):
+        sm, mx, reasons = [], 0.0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx = max(mx, float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for n, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def time_cpu_reference(cfg, n_sample, steps, warmup):
+    """The reference's CPU path (restated, oracle/dau_cpu.c) on n_sample images; images/s."""
+    from oracle import dau_cpu
+    x, e, w, mu1, mu2 = make_inputs_numpy(cfg, n_sample, 77)
+    cores = dau_cpu.load().dau_cpu_num_threads()
+    times = []
+    for it in range(warmup + steps):
+        t0 = time.perf_counter()
+        dau_cpu.forward(x, w, mu1, mu2, 0.5)
+        dau_cpu.backward(x, e, w, mu1, mu2, 0.5)
+        dt = time.perf_counter() - t0
+        if it >= warmup:
+            times.append(dt)
+    tot = sum(times)
+    return n_sample * len(times) / tot, tot / len(times) * 1e3, cores
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    N = CONFIGS[args.config][0]
+    n_sample = args.cpu_sample
+    value, ms, cores = time_cpu_reference(args.config, n_sample, args.steps, min(args.warmup, 1))
+    sample = "%d of the %d images of the per-GPU batch per step (all other sizes unchanged)" % (n_sample, N)
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(args.config), "sample": sample},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+def run_ours(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    import dau_conv
+    from dau_conv import _lib
+
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    N, S, F, units, H, W, ks, m = CONFIGS[args.config]
+    G = units[0] * units[1]
+    U = N * F * S * G * H * W                                   # unit-pixels per rank and step
+
+    # FP32-FMA peak of this GPU, measured now (register-resident FFMA chains on every SM)
+    tf, pms = C.c_double(0), C.c_double(0)
+    _lib.check(_lib.lib.dau_measure_fma_peak(local_rank, 20000, C.byref(tf), C.byref(pms)))
+    fma_peak = tf.value
+
+    xh, eh, wh, m1h, m2h = make_inputs_numpy(args.config, N, 1234 + rank)
+    _, _, wh, m1h, m2h = make_inputs_numpy(args.config, 1, 1234)     # parameters identical on all ranks
+    x, e, w, mu1, mu2 = [torch.from_numpy(a).to(dev) for a in (xh, eh, wh, m1h, m2h)]
+    sigma = torch.full_like(w, 0.5)
+    h = dau_conv.get_handle(dev, num_output=F, number_units_x=units[0], number_units_y=units[1],
+                            kernel_size=ks, pad=(ks - 1) // 2)
+    y = torch.empty((N, F, H, W), device=dev)
+    flat = torch.zeros((4, 1, S, G, F), device=dev)              # one buffer: w, mu1, mu2, sigma grads
+    grads = [flat[k] for k in range(4)]
+
+    def step():
+        h.forward(x, w, mu1, mu2, sigma, out=y)
+        flat.zero_()                                             # the op pre-zeroes (grad_op.cpp:202-205)
+        out = h.backward(x, e, w, mu1, mu2, sigma, grads=grads)
+        if world > 1:
+            dist.all_reduce(flat)                                # only the parameter gradients cross GPUs
+        return out
+
+    def sync_all():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    for _ in range(args.warmup):
+        step()
+    sync_all()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if sampler:
+        sampler.start()
+        time.sleep(0.25)
+    launches0 = h.launch_count()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sync_all()
+    ev0.record()
+    for _ in range(args.steps):
+        step()
+    ev1.record()
+    sync_all()
+    ms_total = ev0.elapsed_time(ev1)
+    launches = h.launch_count() - launches0 + args.steps          # + flat.zero_() per step
+    if sampler:
+        sampler.stop()
+    t = torch.tensor([ms_total], device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total = float(t.item())
+    ms_step = ms_total / args.steps
+    value = N * world * args.steps / (ms_total * 1e-3)
+
+    # ---- per-kernel device times (CUDA events on the launching stream), separate short pass ----
+    h.enable_timing(True)
+    acc = {}
+    reps = 3
+    for _ in range(reps):
+        step()
+        torch.cuda.synchronize(dev)
+        for which in (0, 1):
+            for k, v in h.timing(which).items():
+                acc[k] = acc.get(k, 0.0) + v / reps
+    h.enable_timing(False)
+    flops = {"gather_forward": 8.0 * U, "gather_backprop": 8.0 * U, "grad_units": 16.0 * U}
+    top = max(flops, key=lambda k: acc.get(k, 0.0))
+    achieved = flops[top] / (acc[top] * 1e-3) / 1e12
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        try:
+            traffic = json.load(open(tpath)).get(args.config, {}).get(top)
+        except Exception:
+            traffic = None
+    hbm_peak = None
+    try:
+        hbm_peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]
+    except Exception:
+        hbm_peak = 6650.0
+    min_bytes = 4.0 * N * H * W * (3 * S + 2 * F) + 4.0 * 8 * S * G * F
+    kernel_ms_sum = sum(acc.values())
+    roofline = {
+        "bound": "fp32_fma", "kernel": top, "achieved": achieved, "peak": fma_peak, "unit": "TFLOP/s",
+        "frac": achieved / fma_peak, "traffic": traffic,
+        "peak_source": "FP32 FFMA peak measured in this run on this GPU (MEASURED_PEAKS.json has no fp32 figure); "
+                       "the op is a gather-accumulate on CUDA cores, neither HBM- nor tensor-bound",
+        "algorithmic_flops_per_launch": flops[top],
+        "kernel_ms": {k: round(v, 4) for k, v in acc.items()},
+        "step_fraction_of_fma_peak": 32.0 * U / (kernel_ms_sum * 1e-3) / 1e12 / fma_peak,
+        "hbm": {"algorithmic_bytes_per_step": min_bytes, "achieved_gbs": min_bytes / (kernel_ms_sum * 1e-3) / 1e9,
+                "peak_gbs": hbm_peak, "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)"},
+    }
+
+    # ---- end to end: host buffers in, host buffers out, through the same public API ------------
+    e2e_steps = max(1, min(args.steps, 5))
+    xp, ep = torch.from_numpy(xh).pin_memory(), torch.from_numpy(eh).pin_memory()
+    yp = torch.empty((N, F, H, W), dtype=torch.float32).pin_memory()
+    dxp = torch.empty((N, S, H, W), dtype=torch.float32).pin_memory()
+    gp = torch.empty((4, 1, S, G, F), dtype=torch.float32).pin_memory()
+    xd, ed = torch.empty_like(x), torch.empty_like(e)
+
+    def e2e_step():
+        xd.copy_(xp, non_blocking=True)
+        ed.copy_(ep, non_blocking=True)
+        h.forward(xd, w, mu1, mu2, sigma, out=y)
+        flat.zero_()
+        out = h.backward(xd, ed, w, mu1, mu2, sigma, grads=grads)
+        if world > 1:
+            dist.all_reduce(flat)
+        yp.copy_(y, non_blocking=True)
+        dxp.copy_(out[0], non_blocking=True)
+        gp.copy_(flat, non_blocking=True)
+
+    e2e_step()
+    sync_all()
+    ev0.record()
+    for _ in range(e2e_steps):
+        e2e_step()
+    ev1.record()
+    sync_all()
+    t = torch.tensor([ev0.elapsed_time(ev1)], device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = N * world * e2e_steps / (float(t.item()) * 1e-3)
+    h2d = xh.nbytes + eh.nbytes
+    d2h = yp.numel() * 4 + dxp.numel() * 4 + gp.numel() * 4
+
+    if rank != 0:
+        return
+    cpu_baseline = None
+    if world == 1 and not args.no_cpu_baseline:
+        v, ms, cores = time_cpu_reference(args.config, args.cpu_sample, 1, 0)
+        cpu_baseline = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                        "sample": "%d of the %d images of the batch, one fwd+bwd pass (%.1f s); oracle/dau_cpu.c, "
+                                  "C/OpenMP restatement of the reference CPU path" % (args.cpu_sample, N, ms / 1e3)}
+    print(json.dumps({
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(args.config), "global_batch": N * world,
+                   "parallelism": "batch-sharded dp%d, NCCL all-reduce of [4,S,G,F] parameter gradients" % world,
+                   "l2": "inputs larger than L2 (x and top_error are %.0f MB each; L2 is 126 MB)" % (xh.nbytes / 1e6)},
+        "roofline": roofline, "cpu_baseline": cpu_baseline,
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "steps": e2e_steps, "what": "pinned host x, top_error -> device; fwd+bwd; y, dL/dx and the "
+                                             "4 parameter gradients -> pinned host"},
+        "gpu_launches": launches, "clocks": sampler.summary() if sampler else None,
+    }))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="c2", choices=sorted(CONFIGS))
+    ap.add_argument("--cpu-sample", type=int, default=4, help="images per CPU-baseline pass")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    try:
+        run_ours(args, rank, world, local_rank)
+    finally:
+        if world > 1:
+            import torch.distributed as dist
+            dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

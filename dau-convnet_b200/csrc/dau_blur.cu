@@ -26,15 +26,20 @@ struct BlurArgsBank { float h[3][kMaxBlurTaps]; float v[3][kMaxBlurTaps]; };
 // MODE 0: one separable filter, one output plane per input plane.
 // MODE 1: derivative bank, four output planes [w, mu1, mu2, sigma] per input plane,
 //         laid out [plane][4][H][W] (the reference's [N*S, K, H, W], base_dau_conv_layer.cu:210-221).
+// MODE 2: one separable filter, output in the paired gather layout PG[n/2][c][y][x%4][x/4][n%2]
+//         consumed by dau_gather_tma.cu; planes >= N*Cn (the phantom image of an odd batch) and
+//         the pad columns x in [W, 4*ceil(W/4)) are written as zeros.
 template <int MODE>
 __global__ void __launch_bounds__(256)
 blur_kernel(const float* __restrict__ in, float* __restrict__ out, int H, int W, int kb,
-            const __grid_constant__ BlurArgs1 a1, const __grid_constant__ BlurArgsBank ab) {
-    constexpr int NH = MODE == 0 ? 1 : 3;
+            const __grid_constant__ BlurArgs1 a1, const __grid_constant__ BlurArgsBank ab,
+            int plane0, int N, int Cn) {
+    constexpr int NH = MODE == 1 ? 3 : 1;
     __shared__ float s_in[BIN][BIN + 1];
     __shared__ float s_h[NH][BIN][BT + 1];
     const int c = kb >> 1;
-    const int plane = blockIdx.z;
+    const int plane = plane0 + blockIdx.z;
+    const bool phantom = MODE == 2 && plane >= N * Cn;
     const int x0 = blockIdx.x * BT, y0 = blockIdx.y * BT;
     const float* src = in + (size_t)plane * H * W;
     const int tid = threadIdx.x;
@@ -44,7 +49,7 @@ blur_kernel(const float* __restrict__ in, float* __restrict__ out, int H, int W,
         const int r = i / span, q = i - r * span;
         const int gy = y0 + r - c, gx = x0 + q - c;
         float v = 0.f;
-        if (gy >= 0 && gy < H && gx >= 0 && gx < W) v = __ldg(src + (size_t)gy * W + gx);
+        if (!phantom && gy >= 0 && gy < H && gx >= 0 && gx < W) v = __ldg(src + (size_t)gy * W + gx);
         s_in[r][q] = v;
     }
     __syncthreads();
@@ -56,7 +61,7 @@ blur_kernel(const float* __restrict__ in, float* __restrict__ out, int H, int W,
         for (int j = 0; j < NH; ++j) acc[j] = 0.f;
         for (int u = 0; u < kb; ++u) {
             const float v = s_in[r][q + u];
-            if (MODE == 0) acc[0] = fmaf(v, a1.fx[u], acc[0]);
+            if (MODE != 1) acc[0] = fmaf(v, a1.fx[u], acc[0]);
             else {
 #pragma unroll
                 for (int j = 0; j < NH; ++j) acc[j] = fmaf(v, ab.h[j][u], acc[j]);
@@ -70,6 +75,17 @@ blur_kernel(const float* __restrict__ in, float* __restrict__ out, int H, int W,
     for (int i = tid; i < BT * BT; i += 256) {
         const int r = i / BT, q = i - r * BT;
         const int gy = y0 + r, gx = x0 + q;
+        if (MODE == 2) {
+            const int qv = (W + 3) >> 2, qp = (qv + 1) & ~1;
+            if (gy >= H || gx >= 4 * qv) continue;
+            float acc = 0.f;
+            if (gx < W)
+                for (int v = 0; v < kb; ++v) acc = fmaf(s_h[0][r + v][q], a1.fy[v], acc);
+            const int n = plane / Cn, cn = plane - n * Cn;
+            const size_t row = ((size_t)(n >> 1) * Cn + cn) * H + gy;
+            out[((row * 4 + (gx & 3)) * qp + (gx >> 2)) * 2 + (n & 1)] = acc;
+            continue;
+        }
         if (gy >= H || gx >= W) continue;
         if (MODE == 0) {
             float acc = 0.f;
@@ -106,7 +122,21 @@ void launch_blur_single(const float* in, float* out, int planes, int H, int W, i
     for (int p0 = 0; p0 < planes; p0 += 65535) {
         const int np = planes - p0 < 65535 ? planes - p0 : 65535;
         blur_kernel<0><<<blur_grid(np, H, W), 256, 0, stream>>>(
-            in + (size_t)p0 * H * W, out + (size_t)p0 * H * W, H, W, kb, a1, ab);
+            in + (size_t)p0 * H * W, out + (size_t)p0 * H * W, H, W, kb, a1, ab, 0, 0, 1);
+    }
+    DAU_CUDA_CHECK(cudaGetLastError());
+}
+
+void launch_blur_single_paired(const float* in, float* out_paired, int N, int Cn, int H, int W, int kb,
+                               const float* fx, const float* fy, cudaStream_t stream) {
+    BlurArgs1 a1; BlurArgsBank ab;
+    memset(&a1, 0, sizeof(a1)); memset(&ab, 0, sizeof(ab));
+    for (int i = 0; i < kb; ++i) { a1.fx[i] = fx[i]; a1.fy[i] = fy[i]; }
+    const int planes = ((N + 1) / 2) * 2 * Cn;          // includes the phantom image of an odd batch
+    for (int p0 = 0; p0 < planes; p0 += 65535) {
+        const int np = planes - p0 < 65535 ? planes - p0 : 65535;
+        // `in` is indexed with the absolute plane number inside the kernel
+        blur_kernel<2><<<blur_grid(np, H, W), 256, 0, stream>>>(in, out_paired, H, W, kb, a1, ab, p0, N, Cn);
     }
     DAU_CUDA_CHECK(cudaGetLastError());
 }
@@ -122,7 +152,7 @@ void launch_blur_bank(const float* in, float* out4, int planes, int H, int W,
     for (int p0 = 0; p0 < planes; p0 += 65535) {
         const int np = planes - p0 < 65535 ? planes - p0 : 65535;
         blur_kernel<1><<<blur_grid(np, H, W), 256, 0, stream>>>(
-            in + (size_t)p0 * H * W, out4 + (size_t)p0 * 4 * H * W, H, W, f.kb, a1, ab);
+            in + (size_t)p0 * H * W, out4 + (size_t)p0 * 4 * H * W, H, W, f.kb, a1, ab, 0, 0, 1);
     }
     DAU_CUDA_CHECK(cudaGetLastError());
 }

@@ -226,6 +226,7 @@ GatherPlan plan_gather(int N, int Cin, int Cout, int G, int H, int W, int max_of
     double best_cost = 1e300;
     for (int shape = 0; shape < kNumShapes; ++shape) {
         GatherPlan pl; memset(&pl, 0, sizeof(pl));
+        pl.kind = 0; pl.nstage = 2;
         pl.variant = hclass * kNumShapes + shape;
         DAU_FOR_VARIANT(pl.variant, fill_plan<GEO>(pl));
         const long tx = (W + pl.tile_w - 1) / pl.tile_w, ty = (H + pl.tile_h - 1) / pl.tile_h;

@@ -1,0 +1,263 @@
+// Displaced bilinear gather-accumulate, TMA + packed-FFMA2 variant for sm_100a (images wider
+// than 32 px).  Same math and reference mapping as dau_gather.cu; what changes is how operands
+// move:
+//
+//  * the producing blur kernel writes its output in the "paired gather layout"
+//        PG[n/2][c][y][x%4][x/4][n%2]
+//    so that (a) a haloed tile of an image PAIR is one 4-D TMA box
+//    (cp.async.bulk.tensor, zero fill outside the image = the reference's zero padding of the
+//    blurred input, dau_conv_forward_core.hpp:1707-1710), landing in shared memory already
+//    column-de-interleaved, and (b) one LDS.64 fetches the same pixel of two images;
+//  * a dedicated producer warp streams input channels through an NSTAGE ring of
+//    {tile, unit records} guarded by full/empty mbarriers; the 8 consumer warps never execute a
+//    load instruction for global memory and never meet at a CTA barrier;
+//  * the math is fma.rn.f32x2 (FFMA2): both images of the pair share the unit's weights, so
+//    one instruction issues two FMAs -- the kernel is bound by shared-memory wavefronts
+//    (45 LDS.64 per 128 FFMA2 per lane), not by instruction issue.
+//
+// CTA = 8 consumer warps (8 output channels) + 1 producer warp; tile = 16 x 64 pixels x 2
+// images; lane = (lx 0..15, ly 0..1) owning an 8 x 4 strip of both images (64 accumulators).
+#include "dau_geom.cuh"
+#include "dau_tma.cuh"
+
+#include <cstdlib>
+
+namespace dau {
+
+namespace {
+
+using namespace tma;
+
+constexpr int R = 8, C = 4, LX = 16, LY = 2, NW = 8;
+constexpr int TW = LX * C, TH = LY * R;
+
+template <int HALO>
+struct TGeom {
+    static constexpr int HX = (HALO + 3) / 4 * 4, HY = HALO;
+    static constexpr int QS = (TW + 2 * HX) / 4;          // float2 per column plane
+    static constexpr int THH = TH + 2 * HY;
+    static constexpr int ROW = 4 * QS;                    // float2 per tile row
+    static constexpr int TILE_BYTES = THH * ROW * 8;
+};
+
+struct TGatherParams {
+    const UnitRec* table; const float* bias; float* out;
+    int N, Cin, Cout, G, H, W;
+    int tiles_x, nstage;
+    int stage_bytes;       // tile + records, multiple of 128
+    int debug;
+};
+
+template <int HALO>
+__global__ void __launch_bounds__((NW + 1) * 32, 1)
+dau_gather_tma_kernel(const __grid_constant__ CUtensorMap in_map, const TGatherParams p) {
+    using GEO = TGeom<HALO>;
+    constexpr int QS = GEO::QS, ROW = GEO::ROW;
+    extern __shared__ unsigned char smem_dyn[];
+    __shared__ uint64_t full_bar[8], empty_bar[8];
+    // TMA destinations must be 128-byte aligned; the dynamic segment carries 128 spare bytes
+    unsigned char* smem_raw = smem_dyn + ((128u - (smem_u32(smem_dyn) & 127u)) & 127u);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int tyi = blockIdx.x / p.tiles_x, txi = blockIdx.x - tyi * p.tiles_x;
+    const int x0 = txi * TW, y0 = tyi * TH;
+    const int np = blockIdx.z;                 // image pair
+    const int co0 = blockIdx.y * NW;
+    const int nrec = min(NW, p.Cout - co0) * p.G;
+    const int nstage = p.nstage;
+
+    if (tid == 0) {
+        for (int s = 0; s < nstage; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], NW); }
+        fence_barrier_init();
+    }
+    __syncthreads();
+
+    if (warp == NW) {
+        // ---- producer warp: one lane streams the input channels --------------------------------
+        if (lane == 0) {
+            if (!(p.debug & 1)) prefetch_map(&in_map);
+            const uint32_t tx_bytes = ((p.debug & 2) ? 0 : GEO::TILE_BYTES) + ((p.debug & 4) ? 0 : nrec * (uint32_t)sizeof(UnitRec));
+            for (int ci = 0; ci < p.Cin; ++ci) {
+                const int st = ci % nstage, use = ci / nstage;
+                if (use > 0) mbar_wait(&empty_bar[st], (use - 1) & 1);
+                unsigned char* dst = smem_raw + (size_t)st * p.stage_bytes;
+                mbar_arrive_expect_tx(&full_bar[st], tx_bytes);
+                if (!(p.debug & 2)) tensor4_g2s(dst, &in_map, 2 * ((x0 - GEO::HX) / 4), 0, y0 - GEO::HY, np * p.Cin + ci, &full_bar[st]);
+                if (!(p.debug & 4)) bulk_g2s(dst + GEO::TILE_BYTES, p.table + ((size_t)ci * p.Cout + co0) * p.G,
+                         nrec * (uint32_t)sizeof(UnitRec), &full_bar[st]);
+            }
+        }
+        return;
+    }
+
+    // ---- consumer warps ---------------------------------------------------------------------------
+    const int lx = lane & (LX - 1), ly = lane >> 4;
+    const int co = co0 + warp;
+    const bool co_valid = co < p.Cout;
+    float2 acc[R][C];
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+#pragma unroll
+        for (int c = 0; c < C; ++c) acc[r][c] = make_float2(0.f, 0.f);
+
+    const int lane_base = ly * R * ROW + lx;
+    for (int ci = 0; ci < p.Cin; ++ci) {
+        const int st = ci % nstage, use = ci / nstage;
+        mbar_wait(&full_bar[st], use & 1);
+        const unsigned char* sbase = smem_raw + (size_t)st * p.stage_bytes;
+        if (co_valid) {
+            const float2* tile = reinterpret_cast<const float2*>(sbase) + lane_base;
+            const UnitRec* recs = reinterpret_cast<const UnitRec*>(sbase + GEO::TILE_BYTES) + warp * p.G;
+            for (int g = 0; g < p.G; ++g) {
+                const float4 wv = *reinterpret_cast<const float4*>(&recs[g]);
+                const int2 off = *reinterpret_cast<const int2*>(&recs[g].offx_h);
+                const float2 w00 = make_float2(wv.x, wv.x), w01 = make_float2(wv.y, wv.y);
+                const float2 w10 = make_float2(wv.z, wv.z), w11 = make_float2(wv.w, wv.w);
+                const int b = off.x & 3;
+                const float2* base = tile + off.y * ROW + (off.x >> 2);
+                const float2* colp[C + 1];
+#pragma unroll
+                for (int c = 0; c <= C; ++c) {
+                    const int m = b + c;
+                    colp[c] = base + (m & 3) * QS + (m >> 2);
+                }
+#pragma unroll
+                for (int r = 0; r <= R; ++r) {
+                    float2 xv[C + 1];
+#pragma unroll
+                    for (int c = 0; c <= C; ++c) xv[c] = colp[c][r * ROW];
+                    if (r < R) {
+#pragma unroll
+                        for (int c = 0; c < C; ++c) {
+                            acc[r][c] = __ffma2_rn(w00, xv[c], acc[r][c]);
+                            acc[r][c] = __ffma2_rn(w01, xv[c + 1], acc[r][c]);
+                        }
+                    }
+                    if (r > 0) {
+#pragma unroll
+                        for (int c = 0; c < C; ++c) {
+                            acc[r - 1][c] = __ffma2_rn(w10, xv[c], acc[r - 1][c]);
+                            acc[r - 1][c] = __ffma2_rn(w11, xv[c + 1], acc[r - 1][c]);
+                        }
+                    }
+                }
+            }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty_bar[st]);
+    }
+
+    // ---- epilogue: each image of the pair is stored once, float4 per row --------------------------
+    if (!co_valid) return;
+    const float bv = p.bias ? __ldg(p.bias + co) : 0.f;
+    const int xs = x0 + lx * C;
+    const int H = p.H, W = p.W;
+    const bool vec = ((W & 3) == 0) && (xs + C <= W);
+#pragma unroll
+    for (int img = 0; img < 2; ++img) {
+        const int n = 2 * np + img;
+        if (n >= p.N) break;
+        float* obase = p.out + ((size_t)n * p.Cout + co) * (size_t)H * W;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int y = y0 + ly * R + r;
+            if (y >= H) continue;
+            float v[C];
+#pragma unroll
+            for (int c = 0; c < C; ++c) v[c] = (img == 0 ? acc[r][c].x : acc[r][c].y) + bv;
+            float* orow = obase + (size_t)y * W;
+            if (vec) {
+                *reinterpret_cast<float4*>(orow + xs) = make_float4(v[0], v[1], v[2], v[3]);
+            } else {
+#pragma unroll
+                for (int c = 0; c < C; ++c)
+                    if (xs + c < W) orow[xs + c] = v[c];
+            }
+        }
+    }
+}
+
+constexpr int kHalos[4] = {4, 8, 16, 32};
+
+template <int HALO>
+void launch_t(const GatherPlan& plan, const CUtensorMap& map, const TGatherParams& p, cudaStream_t stream) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        DAU_CUDA_CHECK(cudaFuncSetAttribute(dau_gather_tma_kernel<HALO>,
+                                            cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+        attr_set = true;
+    }
+    dim3 grid(plan.grid_x, plan.grid_y, plan.grid_z);
+    dau_gather_tma_kernel<HALO><<<grid, (NW + 1) * 32, plan.smem_bytes, stream>>>(map, p);
+}
+
+template <int HALO>
+void fill_t(GatherPlan& pl) {
+    using GEO = TGeom<HALO>;
+    pl.halo_x = GEO::HX; pl.halo_y = GEO::HY;
+    pl.row_stride = GEO::ROW * 2; pl.img_stride = 0;
+    pl.stage_words = GEO::TILE_BYTES / 4;
+}
+
+}  // namespace
+
+size_t paired_layout_floats(int N, int Cn, int H, int W) {
+    const size_t qv = (W + 3) / 4, qp = (qv + 1) / 2 * 2;
+    return (size_t)((N + 1) / 2) * Cn * H * 4 * qp * 2;
+}
+
+bool plan_gather_tma(int N, int Cin, int Cout, int G, int H, int W, int max_off, GatherPlan* out) {
+    if (W <= 32) return false;                    // narrower images use the cp.async kernel (dau_gather.cu)
+    int hclass = 0;
+    while (kHalos[hclass] < max_off) ++hclass;
+    GatherPlan pl; memset(&pl, 0, sizeof(pl));
+    pl.kind = 1; pl.variant = hclass;
+    pl.tile_w = TW; pl.tile_h = TH; pl.imgs = 2; pl.cout_per_cta = NW;
+    switch (hclass) {
+        case 0: fill_t<4>(pl); break;
+        case 1: fill_t<8>(pl); break;
+        case 2: fill_t<16>(pl); break;
+        default: fill_t<32>(pl); break;
+    }
+    const size_t tile_bytes = (size_t)pl.stage_words * 4;
+    const size_t stage = (tile_bytes + (size_t)NW * G * sizeof(UnitRec) + 127) / 128 * 128;
+    int nstage = (int)((200 * 1024 - 128) / stage);
+    if (nstage > 4) nstage = 4;
+    if (nstage < 2) return false;
+    pl.stage_words = (int)(stage / 4);
+    pl.nstage = nstage;
+    pl.smem_bytes = stage * nstage + 128;
+    pl.grid_x = ((W + TW - 1) / TW) * ((H + TH - 1) / TH);
+    pl.grid_y = (Cout + NW - 1) / NW;
+    pl.grid_z = (N + 1) / 2;
+    if (pl.grid_y > 65535 || pl.grid_z > 65535) return false;
+    (void)Cin;
+    *out = pl;
+    return true;
+}
+
+void launch_gather_tma(const GatherPlan& plan, const float* in_paired, const UnitRec* table, const float* bias,
+                       float* out, int N, int Cin, int Cout, int G, int H, int W, cudaStream_t stream) {
+    // tensor map of the paired gather layout: dims (q*2+i, p, y, plane)
+    const uint64_t qv = (W + 3) / 4, qp = (qv + 1) / 2 * 2;
+    const uint64_t dims[4] = {2 * qv, 4, (uint64_t)H, (uint64_t)((N + 1) / 2) * Cin};
+    const uint64_t strides[3] = {qp * 8, 4 * qp * 8, (uint64_t)H * 4 * qp * 8};
+    const int halo_q2 = 2 * ((TW + 2 * plan.halo_x) / 4);
+    const uint32_t box[4] = {(uint32_t)halo_q2, 4, (uint32_t)(TH + 2 * plan.halo_y), 1};
+    const CUtensorMap map = make_map_f32(in_paired, 4, dims, strides, box);
+    TGatherParams p;
+    p.table = table; p.bias = bias; p.out = out;
+    p.N = N; p.Cin = Cin; p.Cout = Cout; p.G = G; p.H = H; p.W = W;
+    p.tiles_x = (W + TW - 1) / TW; p.nstage = plan.nstage;
+    p.stage_bytes = plan.stage_words * 4;
+    p.debug = getenv("DAU_DEBUG") ? atoi(getenv("DAU_DEBUG")) : 0;
+    switch (plan.variant) {
+        case 0: launch_t<4>(plan, map, p, stream); break;
+        case 1: launch_t<8>(plan, map, p, stream); break;
+        case 2: launch_t<16>(plan, map, p, stream); break;
+        default: launch_t<32>(plan, map, p, stream); break;
+    }
+    DAU_CUDA_CHECK(cudaGetLastError());
+}
+
+}  // namespace dau

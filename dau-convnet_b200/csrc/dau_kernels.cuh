@@ -49,6 +49,9 @@ void launch_blur_bank(const float* in, float* out4, int planes, int H, int W,
 
 // ---- displaced gather (forward and dL/dx) -------------------------------------------------
 struct GatherPlan {            // chosen once per shape by plan_gather()
+    int kind;                  // 0: cp.async kernel on NCHW input (dau_gather.cu)
+                               // 1: TMA + FFMA2 kernel on the paired gather layout (dau_gather_tma.cu)
+    int nstage;                // pipeline depth (kind 1)
     int variant;               // index into the instantiated tile shapes
     int tile_w, tile_h, imgs;  // output tile of one CTA: imgs x tile_h x tile_w
     int halo_x, halo_y;
@@ -62,6 +65,15 @@ GatherPlan plan_gather(int N, int Cin, int Cout, int G, int H, int W, int max_of
 // out[n,co,y,x] = sum_{ci,g} gather(in[n,ci], table[ci][co][g]) (+ bias[co])
 void launch_gather(const GatherPlan& p, const float* in, const UnitRec* table, const float* bias,
                    float* out, int N, int Cin, int Cout, int G, int H, int W, cudaStream_t stream);
+
+// TMA variant: `in_paired` is the blurred input in the paired gather layout
+//   PG[n/2][c][y][x%4][x/4][n%2]   (x/4 padded to an even count; written by launch_blur_single_paired)
+size_t paired_layout_floats(int N, int Cn, int H, int W);
+bool plan_gather_tma(int N, int Cin, int Cout, int G, int H, int W, int max_off, GatherPlan* out);
+void launch_gather_tma(const GatherPlan& p, const float* in_paired, const UnitRec* table, const float* bias,
+                       float* out, int N, int Cin, int Cout, int G, int H, int W, cudaStream_t stream);
+void launch_blur_single_paired(const float* in, float* out_paired, int N, int Cn, int H, int W, int kb,
+                               const float* fx, const float* fy, cudaStream_t stream);
 
 // ---- parameter gradients -----------------------------------------------------------------
 struct GradPlan {

@@ -60,19 +60,22 @@ void DAUConvLayerB200::Reshape(int N, int S, int H, int W, size_t* fwd_ws, size_
     N_ = N; S_ = S; H_ = H; W_ = W;
     const size_t act_in = (size_t)N * S * H * W, act_out = (size_t)N * F_ * H * W;
     const size_t units = (size_t)S * G_ * F_;
-    fwd_plan_ = plan_gather(N, S, F_, G_, H, W, max_off_);
-    bwd_plan_ = plan_gather(N, F_, S, G_, H, W, max_off_);
+    // wide images: TMA + FFMA2 kernel on the paired gather layout; otherwise the cp.async kernel
+    if (!plan_gather_tma(N, S, F_, G_, H, W, max_off_, &fwd_plan_)) fwd_plan_ = plan_gather(N, S, F_, G_, H, W, max_off_);
+    if (!plan_gather_tma(N, F_, S, G_, H, W, max_off_, &bwd_plan_)) bwd_plan_ = plan_gather(N, F_, S, G_, H, W, max_off_);
     grad_plan_ = plan_grad(N, S, F_, G_, H, W, max_off_, num_sms_);
     // forward workspace: blurred input | unit table | flag
     size_t o = 0;
-    off_fwd_blur_ = o;  o = align_up(o + act_in * sizeof(float));
+    const size_t blur_in = fwd_plan_.kind == 1 ? paired_layout_floats(N, S, H, W) : act_in;
+    const size_t blur_out = bwd_plan_.kind == 1 ? paired_layout_floats(N, F_, H, W) : act_out;
+    off_fwd_blur_ = o;  o = align_up(o + blur_in * sizeof(float));
     off_fwd_table_ = o; o = align_up(o + units * sizeof(UnitRec));
     off_fwd_flag_ = o;  o = align_up(o + 256);
     fwd_ws_ = o;
     // backward workspace: 4 derivative blurs | blurred error | two unit tables | split partials | flag
     o = 0;
     off_bwd_xk_ = o;      o = align_up(o + 4 * act_in * sizeof(float));
-    off_bwd_eb_ = o;      o = align_up(o + act_out * sizeof(float));
+    off_bwd_eb_ = o;      o = align_up(o + blur_out * sizeof(float));
     off_bwd_table_ = o;   o = align_up(o + units * sizeof(UnitRec));
     off_bwd_gtable_ = o;  o = align_up(o + units * sizeof(UnitRec));
     off_bwd_partial_ = o; o = align_up(o + grad_plan_.partial_floats * sizeof(float));
@@ -170,7 +173,8 @@ void DAUConvLayerB200::Forward_gpu(const float* bottom, float* w, float* mu1, fl
     const BlurFactors& f = factors_for(sigma, stream);
 
     tic(0, 1, stream);
-    launch_blur_single(bottom, xb, N_ * S_, H_, W_, f.kb, f.fwd_x, f.fwd_y, stream);
+    if (fwd_plan_.kind == 1) launch_blur_single_paired(bottom, xb, N_, S_, H_, W_, f.kb, f.fwd_x, f.fwd_y, stream);
+    else launch_blur_single(bottom, xb, N_ * S_, H_, W_, f.kb, f.fwd_x, f.fwd_y, stream);
     toc(0, 1, stream);
 
     tic(0, 2, stream);
@@ -183,7 +187,10 @@ void DAUConvLayerB200::Forward_gpu(const float* bottom, float* w, float* mu1, fl
     toc(0, 2, stream);
 
     tic(0, 3, stream);
-    launch_gather(fwd_plan_, xb, table, st_.bias_term ? bias : nullptr, top, N_, S_, F_, G_, H_, W_, stream);
+    if (fwd_plan_.kind == 1)
+        launch_gather_tma(fwd_plan_, xb, table, st_.bias_term ? bias : nullptr, top, N_, S_, F_, G_, H_, W_, stream);
+    else
+        launch_gather(fwd_plan_, xb, table, st_.bias_term ? bias : nullptr, top, N_, S_, F_, G_, H_, W_, stream);
     toc(0, 3, stream);
 }
 
@@ -251,10 +258,14 @@ void DAUConvLayerB200::Backward_gpu(const float* bottom, const float* top_error,
         // blur the error with the rotated filter, then gather with -mu and the parameters read
         // transposed (base_dau_conv_layer.cu:278-325)
         tic(1, 4, stream);
-        launch_blur_single(top_error, eb, N_ * F_, H_, W_, f.kb, f.err_x, f.err_y, stream);
+        if (bwd_plan_.kind == 1) launch_blur_single_paired(top_error, eb, N_, F_, H_, W_, f.kb, f.err_x, f.err_y, stream);
+        else launch_blur_single(top_error, eb, N_ * F_, H_, W_, f.kb, f.err_x, f.err_y, stream);
         toc(1, 4, stream);
         tic(1, 5, stream);
-        launch_gather(bwd_plan_, eb, btable, nullptr, bottom_error, N_, F_, S_, G_, H_, W_, stream);
+        if (bwd_plan_.kind == 1)
+            launch_gather_tma(bwd_plan_, eb, btable, nullptr, bottom_error, N_, F_, S_, G_, H_, W_, stream);
+        else
+            launch_gather(bwd_plan_, eb, btable, nullptr, bottom_error, N_, F_, S_, G_, H_, W_, stream);
         toc(1, 5, stream);
     }
     if ((flags & DAU_GRAD_BIAS) && st_.bias_term && dbias) {
