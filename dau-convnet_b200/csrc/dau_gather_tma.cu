@@ -33,7 +33,8 @@ constexpr int TW = LX * C, TH = LY * R;
 
 template <int HALO>
 struct TGeom {
-    static constexpr int HX = (HALO + 3) / 4 * 4, HY = HALO;
+    // the innermost TMA start coordinate must be 16-byte aligned: 2*(x0-HX)/4 floats -> HX % 8 == 0
+    static constexpr int HX = (HALO + 7) / 8 * 8, HY = HALO;
     static constexpr int QS = (TW + 2 * HX) / 4;          // float2 per column plane
     static constexpr int THH = TH + 2 * HY;
     static constexpr int ROW = 4 * QS;                    // float2 per tile row

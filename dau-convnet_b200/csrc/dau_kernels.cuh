@@ -29,7 +29,8 @@ struct UnitPrepArgs {
     const float* w; const float* mu1; const float* mu2;   // [1,S,G,F]
     int S, G, F;
     int g_active;            // G - number_units_ignore
-    int halo_x, halo_y;      // halo_x is rounded up to the column-interleave factor
+    int halo_x, halo_y;      // halo of the forward / back-propagation tables (x halo is rounded up by the kernel)
+    int ghalo_x, ghalo_y;    // halo of the gradient table (its kernel may round differently)
     int max_off;             // kernel_size/2: integer offsets are clamped to [-max_off, max_off-1]
     int use_interpolation;
 };

@@ -182,6 +182,7 @@ void DAUConvLayerB200::Forward_gpu(const float* bottom, float* w, float* mu1, fl
     ua.w = w; ua.mu1 = mu1; ua.mu2 = mu2; ua.S = S_; ua.G = G_; ua.F = F_;
     ua.g_active = G_ - st_.number_units_ignore;
     ua.halo_x = fwd_plan_.halo_x; ua.halo_y = fwd_plan_.halo_y; ua.max_off = max_off_;
+    ua.ghalo_x = ua.halo_x; ua.ghalo_y = ua.halo_y;
     ua.use_interpolation = st_.use_interpolation;
     launch_unit_prep(ua, table, nullptr, nullptr, flag, stream);
     toc(0, 2, stream);
@@ -228,11 +229,10 @@ void DAUConvLayerB200::Backward_gpu(const float* bottom, const float* top_error,
         toc(1, 0, stream);
     }
     {
-        // both tables in one launch (their halos are the same by construction: same halo class)
+        // both tables in one launch
         tic(1, 1, stream);
-        ua.halo_x = grad_plan_.halo_x; ua.halo_y = grad_plan_.halo_y;
-        DAU_CHECK(bwd_plan_.halo_x == grad_plan_.halo_x && bwd_plan_.halo_y == grad_plan_.halo_y, 3,
-                  "internal: halo mismatch between back-propagation and gradient plans");
+        ua.halo_x = bwd_plan_.halo_x; ua.halo_y = bwd_plan_.halo_y;
+        ua.ghalo_x = grad_plan_.halo_x; ua.ghalo_y = grad_plan_.halo_y;
         launch_unit_prep(ua, nullptr, want_input ? btable : nullptr, want_params ? gtable : nullptr, flag, stream);
         toc(1, 1, stream);
     }

@@ -49,7 +49,7 @@ __global__ void unit_prep_kernel(UnitPrepArgs a, UnitRec* __restrict__ fwd, Unit
         // gather of the ERROR around p' - o - 1 (see dau_grad.cu); tap order flips
         UnitRec r;
         r.w00 = b11; r.w01 = b10; r.w10 = b01; r.w11 = b00;
-        r.offx_h = -ox - 1 + a.halo_x; r.offy_h = -oy - 1 + a.halo_y; r.pad0 = 0; r.pad1 = 0;
+        r.offx_h = -ox - 1 + a.ghalo_x; r.offy_h = -oy - 1 + a.ghalo_y; r.pad0 = 0; r.pad1 = 0;
         grad[((size_t)s * a.F + f) * a.G + g] = r;
     }
     if (bwd) {

@@ -65,6 +65,14 @@ int main(int argc, char** argv) {
         CUtensorMap m = make_map_f32(d, 4, dims, str, box); nf = 36 * 4 * 8;
         k4<<<1, 128, 64 * 1024>>>(m, o, -2, 0, 0, 1, nf);
     }
+    else if (mode == 9) {   // generic: d0 d1 d2 d3 b0 b1 b2 b3 c0 c1 c2 c3
+        uint64_t dims[4]; uint32_t box[4]; int c[4];
+        for (int i = 0; i < 4; ++i) { dims[i] = atoi(argv[2 + i]); box[i] = atoi(argv[6 + i]); c[i] = atoi(argv[10 + i]); }
+        uint64_t str[3] = {((dims[0] * 4 + 15) / 16) * 16, 0, 0};
+        str[1] = str[0] * dims[1]; str[2] = str[1] * dims[2];
+        CUtensorMap m = make_map_f32(d, 4, dims, str, box); nf = box[0] * box[1] * box[2] * box[3];
+        k4<<<1, 128, 64 * 1024>>>(m, o, c[0], c[1], c[2], c[3], nf);
+    }
     cudaError_t e = cudaDeviceSynchronize();
     std::vector<float> r(nf);
     cudaMemcpy(r.data(), o, nf * 4, cudaMemcpyDeviceToHost);
