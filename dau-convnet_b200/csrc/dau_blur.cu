@@ -33,8 +33,8 @@ template <int MODE>
 __global__ void __launch_bounds__(256)
 blur_kernel(const float* __restrict__ in, float* __restrict__ out, int H, int W, int kb,
             const __grid_constant__ BlurArgs1 a1, const __grid_constant__ BlurArgsBank ab,
-            int plane0, int N, int Cn) {
-    constexpr int NH = MODE == 1 ? 3 : 1;
+            int plane0, int N, int Cn, int tiles_x, int tiles_y) {
+    constexpr int NH = (MODE == 1 || MODE == 3) ? 3 : 1;
     __shared__ float s_in[BIN][BIN + 1];
     __shared__ float s_h[NH][BIN][BT + 1];
     const int c = kb >> 1;
@@ -61,7 +61,7 @@ blur_kernel(const float* __restrict__ in, float* __restrict__ out, int H, int W,
         for (int j = 0; j < NH; ++j) acc[j] = 0.f;
         for (int u = 0; u < kb; ++u) {
             const float v = s_in[r][q + u];
-            if (MODE != 1) acc[0] = fmaf(v, a1.fx[u], acc[0]);
+            if (NH == 1) acc[0] = fmaf(v, a1.fx[u], acc[0]);
             else {
 #pragma unroll
                 for (int j = 0; j < NH; ++j) acc[j] = fmaf(v, ab.h[j][u], acc[j]);
@@ -84,6 +84,26 @@ blur_kernel(const float* __restrict__ in, float* __restrict__ out, int H, int W,
             const int n = plane / Cn, cn = plane - n * Cn;
             const size_t row = ((size_t)(n >> 1) * Cn + cn) * H + gy;
             out[((row * 4 + (gx & 3)) * qp + (gx >> 2)) * 2 + (n & 1)] = acc;
+            continue;
+        }
+        if (MODE == 3) {
+            // derivative bank in the strip-major layout XS[item][s][k][r(8)][lane(32)][c(2)] of
+            // dau_grad_tma.cu; positions of the last tiles that fall outside the image are zeros
+            if (gy >= tiles_y * 8 || gx >= tiles_x * 64) continue;
+            float aw = 0.f, am1 = 0.f, am2 = 0.f, asg = 0.f;
+            if (gy < H && gx < W)
+                for (int v = 0; v < kb; ++v) {
+                    const float t0 = s_h[0][r + v][q], t1 = s_h[1][r + v][q], t2 = s_h[2][r + v][q];
+                    aw = fmaf(t0, ab.v[0][v], aw);
+                    am1 = fmaf(t1, ab.v[0][v], am1);
+                    am2 = fmaf(t0, ab.v[1][v], am2);
+                    asg = fmaf(t2, ab.v[0][v], asg);
+                    asg = fmaf(t0, ab.v[2][v], asg);
+                }
+            const int n = plane / Cn, cn = plane - n * Cn;
+            const size_t item = ((size_t)n * tiles_y + (gy >> 3)) * tiles_x + (gx >> 6);
+            float* o = out + ((item * Cn + cn) * 4 * 8 + (gy & 7)) * 64 + (gx & 63);
+            o[0] = aw; o[8 * 64] = am1; o[2 * 8 * 64] = am2; o[3 * 8 * 64] = asg;
             continue;
         }
         if (gy >= H || gx >= W) continue;
@@ -122,7 +142,7 @@ void launch_blur_single(const float* in, float* out, int planes, int H, int W, i
     for (int p0 = 0; p0 < planes; p0 += 65535) {
         const int np = planes - p0 < 65535 ? planes - p0 : 65535;
         blur_kernel<0><<<blur_grid(np, H, W), 256, 0, stream>>>(
-            in + (size_t)p0 * H * W, out + (size_t)p0 * H * W, H, W, kb, a1, ab, 0, 0, 1);
+            in + (size_t)p0 * H * W, out + (size_t)p0 * H * W, H, W, kb, a1, ab, 0, 0, 1, 0, 0);
     }
     DAU_CUDA_CHECK(cudaGetLastError());
 }
@@ -136,7 +156,7 @@ void launch_blur_single_paired(const float* in, float* out_paired, int N, int Cn
     for (int p0 = 0; p0 < planes; p0 += 65535) {
         const int np = planes - p0 < 65535 ? planes - p0 : 65535;
         // `in` is indexed with the absolute plane number inside the kernel
-        blur_kernel<2><<<blur_grid(np, H, W), 256, 0, stream>>>(in, out_paired, H, W, kb, a1, ab, p0, N, Cn);
+        blur_kernel<2><<<blur_grid(np, H, W), 256, 0, stream>>>(in, out_paired, H, W, kb, a1, ab, p0, N, Cn, 0, 0);
     }
     DAU_CUDA_CHECK(cudaGetLastError());
 }
@@ -152,7 +172,55 @@ void launch_blur_bank(const float* in, float* out4, int planes, int H, int W,
     for (int p0 = 0; p0 < planes; p0 += 65535) {
         const int np = planes - p0 < 65535 ? planes - p0 : 65535;
         blur_kernel<1><<<blur_grid(np, H, W), 256, 0, stream>>>(
-            in + (size_t)p0 * H * W, out4 + (size_t)p0 * 4 * H * W, H, W, f.kb, a1, ab, 0, 0, 1);
+            in + (size_t)p0 * H * W, out4 + (size_t)p0 * 4 * H * W, H, W, f.kb, a1, ab, 0, 0, 1, 0, 0);
+    }
+    DAU_CUDA_CHECK(cudaGetLastError());
+}
+
+void launch_blur_bank_strips(const float* in, float* out_strips, int N, int S, int H, int W,
+                             const BlurFactors& f, cudaStream_t stream) {
+    BlurArgs1 a1; BlurArgsBank ab;
+    memset(&a1, 0, sizeof(a1)); memset(&ab, 0, sizeof(ab));
+    for (int i = 0; i < f.kb; ++i) {
+        ab.h[0][i] = f.h0[i]; ab.h[1][i] = f.h1[i]; ab.h[2][i] = f.h2[i];
+        ab.v[0][i] = f.v0[i]; ab.v[1][i] = f.v1[i]; ab.v[2][i] = f.v2[i];
+    }
+    const int tx = (W + 63) / 64, ty = (H + 7) / 8;
+    const int planes = N * S;
+    for (int p0 = 0; p0 < planes; p0 += 65535) {
+        const int np = planes - p0 < 65535 ? planes - p0 : 65535;
+        blur_kernel<3><<<blur_grid(np, ty * 8, tx * 64), 256, 0, stream>>>(in, out_strips, H, W, f.kb, a1, ab,
+                                                                            p0, N, S, tx, ty);
+    }
+    DAU_CUDA_CHECK(cudaGetLastError());
+}
+
+namespace {
+// top error NCHW -> SG[n][f][y][x%2][x/2] (row of x/2 padded to a multiple of 4), with the
+// ignore_edge_gradients mask (dau_conv_backward_core.hpp:2218-2222) applied on the way
+__global__ void __launch_bounds__(256) error_relayout_kernel(const float* __restrict__ err, float* __restrict__ out,
+                                                             int H, int W, int qp, int mask_row, int mask_col) {
+    const int plane = blockIdx.y;
+    const int y = blockIdx.x;
+    const float* src = err + ((size_t)plane * H + y) * W;
+    float* dst = out + ((size_t)plane * H + y) * 2 * qp;
+    const bool rowdead = mask_row && y == H - 1;
+    for (int x = threadIdx.x; x < 2 * qp; x += 256) {
+        float v = 0.f;
+        if (x < W && !rowdead && !(mask_col && x == W - 1)) v = __ldg(src + x);
+        dst[(x & 1) * qp + (x >> 1)] = v;
+    }
+}
+}  // namespace
+
+void launch_error_relayout(const float* err, float* out_sg, int planes, int H, int W, int mask_row, int mask_col,
+                           cudaStream_t stream) {
+    const int qv = (W + 1) / 2, qp = (qv + 3) / 4 * 4;
+    for (int p0 = 0; p0 < planes; p0 += 65535) {
+        const int np = planes - p0 < 65535 ? planes - p0 : 65535;
+        error_relayout_kernel<<<dim3(H, np), 256, 0, stream>>>(err + (size_t)p0 * H * W,
+                                                               out_sg + (size_t)p0 * H * 2 * qp, H, W, qp,
+                                                               mask_row, mask_col);
     }
     DAU_CUDA_CHECK(cudaGetLastError());
 }

@@ -285,6 +285,7 @@ GradPlan plan_grad(int N, int S, int F, int G, int H, int W, int max_off, int nu
     double best_cost = 1e300;
     for (int shape = 0; shape < kNumShapes; ++shape) {
         GradPlan pl; memset(&pl, 0, sizeof(pl));
+        pl.kind = 0;
         pl.variant = hclass * kNumShapes + shape;
         DAU_GFOR_VARIANT(pl.variant, fill_plan<GEO>(pl));
         const size_t xk_words = pl.smem_bytes;

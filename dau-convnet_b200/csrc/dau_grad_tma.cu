@@ -1,0 +1,292 @@
+// Per-unit parameter gradients, TMA variant for sm_100a (images wider than 32 px).
+// Same math, operand roles and reference mapping as dau_grad.cu (Xk resident in registers,
+// the error gathered from a haloed shared-memory tile); what changes is how operands move:
+//
+//  * the derivative-blur kernel writes Xk "strip-major":
+//        XS[item][s][k][r][lane][c],  item = (n, tile_y, tile_x), r < 8, c < 2
+//    so that everything the 8 warps (= 8 input channels) of a CTA need for one item is ONE
+//    contiguous 64 KB block fetched by ONE cp.async.bulk;
+//  * the top error is re-laid out once (edge mask applied) as
+//        SG[n][f][y][x%2][x/2]
+//    so that the haloed tile of one (image, feature) is one 4-D TMA box, already column
+//    de-interleaved; 32 lanes x 2 columns cover the 64-px tile, every LDS.32 of the window is a
+//    single conflict-free wavefront whatever the unit's offset;
+//  * a producer warp streams items through a 2-stage ring guarded by full/empty mbarriers;
+//    the consumer warps execute no global loads and meet no CTA barrier.
+//
+// lane strip = 8 rows x 2 columns (16 pixels): 27 LDS per 128 FMA per unit.
+#include "dau_geom.cuh"
+#include "dau_tma.cuh"
+
+namespace dau {
+
+namespace {
+
+using namespace tma;
+
+constexpr int R = 8, C = 2, NW = 8, UPW = 16, TW = 64, TH = 8;
+constexpr int XK_WARP_BYTES = 4 * R * 32 * C * 4;      // 8 KB: [k][r][lane][c]
+
+template <int HALO>
+struct GGeomT {
+    // innermost TMA start coordinate (x0-HX)/2 floats must be a multiple of 4 floats
+    static constexpr int HX = (HALO + 7) / 8 * 8, HY = HALO;
+    static constexpr int QS = (TW + 2 * HX) / 2;       // words per column plane
+    static constexpr int THH = TH + 2 * HY;
+    static constexpr int ROW = 2 * QS;                 // words per tile row
+    static constexpr int FEAT_BYTES = THH * ROW * 4;
+};
+
+struct TGradParams {
+    const float* xs; const UnitRec* table; float* partial;
+    int N, S, F, G;
+    int FC, GC, n_gchunks;
+    int tiles_x, tiles, items, items_per_split;
+    int feat_bytes_al;     // FEAT_BYTES rounded up to 128
+    int stage_bytes;
+};
+
+template <int HALO>
+__global__ void __launch_bounds__((NW + 1) * 32, 1)
+dau_grad_tma_kernel(const __grid_constant__ CUtensorMap err_map, const TGradParams p) {
+    using GEO = GGeomT<HALO>;
+    constexpr int QS = GEO::QS, ROW = GEO::ROW;
+    extern __shared__ unsigned char smem_dyn[];
+    __shared__ uint64_t full_bar[2], empty_bar[2];
+    __shared__ UnitRec s_units[NW][UPW];
+    unsigned char* smem_raw = smem_dyn + ((128u - (smem_u32(smem_dyn) & 127u)) & 127u);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    // f-chunks vary fastest across the grid: CTAs that run together share the Xk block in L2
+    const int fchunk = blockIdx.x / p.n_gchunks, gchunk = blockIdx.x - fchunk * p.n_gchunks;
+    const int s0 = blockIdx.y * NW;
+    const int f0 = fchunk * p.FC, g0 = gchunk * p.GC;
+    const int F = p.F, G = p.G;
+    const int nfeat = min(p.FC, F - f0), ngc = min(p.GC, G - g0);
+    const int nunits = nfeat * ngc;
+    const int nsv = min(NW, p.S - s0);                 // valid input channels of this CTA
+    const int item_begin = blockIdx.z * p.items_per_split;
+    const int item_end = min(p.items, item_begin + p.items_per_split);
+
+    if (tid == 0) {
+        for (int s = 0; s < 2; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], NW); }
+        fence_barrier_init();
+    }
+    if (warp < NW && s0 + warp < p.S && lane < nunits) {
+        const int fi = lane / ngc, gi = lane - fi * ngc;
+        UnitRec r = p.table[((size_t)(s0 + warp) * F + f0 + fi) * G + g0 + gi];
+        r.pad0 = fi * (p.feat_bytes_al / 4);           // word offset of the feature's error tile
+        s_units[warp][lane] = r;
+    }
+    __syncthreads();
+
+    if (warp == NW) {
+        if (lane == 0) {
+            prefetch_map(&err_map);
+            const uint32_t tx = nfeat * GEO::FEAT_BYTES + nsv * XK_WARP_BYTES;
+            for (int item = item_begin; item < item_end; ++item) {
+                const int k = item - item_begin, st = k & 1, use = k >> 1;
+                if (use > 0) mbar_wait(&empty_bar[st], (use - 1) & 1);
+                const int n = item / p.tiles, t = item - n * p.tiles;
+                const int tyi = t / p.tiles_x, txi = t - tyi * p.tiles_x;
+                unsigned char* dst = smem_raw + (size_t)st * p.stage_bytes;
+                mbar_arrive_expect_tx(&full_bar[st], tx);
+                for (int fi = 0; fi < nfeat; ++fi)
+                    tensor4_g2s(dst + fi * p.feat_bytes_al, &err_map, (txi * TW - GEO::HX) / 2, 0,
+                                tyi * TH - GEO::HY, n * F + f0 + fi, &full_bar[st]);
+                bulk_g2s(dst + p.FC * p.feat_bytes_al,
+                         p.xs + ((size_t)item * p.S + s0) * (XK_WARP_BYTES / 4), nsv * XK_WARP_BYTES, &full_bar[st]);
+            }
+        }
+        return;
+    }
+
+    // ---- consumer warps: warp = input channel s0 + warp -------------------------------------------
+    const bool s_valid = warp < nsv;
+    float acc[UPW][4];
+#pragma unroll
+    for (int u = 0; u < UPW; ++u)
+#pragma unroll
+        for (int k = 0; k < 4; ++k) acc[u][k] = 0.f;
+
+    for (int item = item_begin; item < item_end; ++item) {
+        const int kk = item - item_begin, st = kk & 1, use = kk >> 1;
+        mbar_wait(&full_bar[st], use & 1);
+        const unsigned char* sbase = smem_raw + (size_t)st * p.stage_bytes;
+        if (s_valid) {
+            float2 xk[4][R];
+            const float2* xsrc = reinterpret_cast<const float2*>(sbase + p.FC * p.feat_bytes_al +
+                                                                 warp * XK_WARP_BYTES) + lane;
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+#pragma unroll
+                for (int r = 0; r < R; ++r) xk[k][r] = xsrc[(k * R + r) * 32];
+            const float* tb = reinterpret_cast<const float*>(sbase) + lane;
+#pragma unroll
+            for (int u = 0; u < UPW; ++u) {
+                if (u < nunits) {
+                    const UnitRec* rec = &s_units[warp][u];
+                    const float4 wv = *reinterpret_cast<const float4*>(rec);
+                    const int4 off = *reinterpret_cast<const int4*>(&rec->offx_h);   // offx, offy, tile offset
+                    const int b = off.x & 1;
+                    const float* base = tb + off.z + off.y * ROW + (off.x >> 1);
+                    const float* colp[C + 1];
+#pragma unroll
+                    for (int c = 0; c <= C; ++c) {
+                        const int m = b + c;
+                        colp[c] = base + (m & 1) * QS + (m >> 1);
+                    }
+                    float prev[C + 1];
+#pragma unroll
+                    for (int c = 0; c <= C; ++c) prev[c] = colp[c][0];
+#pragma unroll
+                    for (int r = 1; r <= R; ++r) {
+                        float cur[C + 1];
+#pragma unroll
+                        for (int c = 0; c <= C; ++c) cur[c] = colp[c][r * ROW];
+#pragma unroll
+                        for (int c = 0; c < C; ++c) {
+                            float e = wv.x * prev[c];
+                            e = fmaf(wv.y, prev[c + 1], e);
+                            e = fmaf(wv.z, cur[c], e);
+                            e = fmaf(wv.w, cur[c + 1], e);
+#pragma unroll
+                            for (int k = 0; k < 4; ++k)
+                                acc[u][k] = fmaf(e, c == 0 ? xk[k][r - 1].x : xk[k][r - 1].y, acc[u][k]);
+                        }
+#pragma unroll
+                        for (int c = 0; c <= C; ++c) prev[c] = cur[c];
+                    }
+                }
+            }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty_bar[st]);
+    }
+
+    if (s_valid) {
+        const int s = s0 + warp;
+        const size_t sgf = (size_t)p.S * G * F;
+        float* pbase = p.partial + (size_t)blockIdx.z * 4 * sgf;
+#pragma unroll
+        for (int u = 0; u < UPW; ++u) {
+            if (u < nunits) {
+                const int fi = u / ngc, gi = u - fi * ngc;
+                const size_t idx = ((size_t)s * G + g0 + gi) * F + f0 + fi;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    float v = acc[u][k];
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                    if (lane == 0) pbase[(size_t)k * sgf + idx] = v;
+                }
+            }
+        }
+    }
+}
+
+constexpr int kHalos[4] = {4, 8, 16, 32};
+
+template <int HALO>
+void launch_t(const GradPlan& plan, const CUtensorMap& map, const TGradParams& p, cudaStream_t stream) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        DAU_CUDA_CHECK(cudaFuncSetAttribute(dau_grad_tma_kernel<HALO>,
+                                            cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+        attr_set = true;
+    }
+    dim3 grid(plan.grid_x, plan.grid_y, plan.grid_z);
+    dau_grad_tma_kernel<HALO><<<grid, (NW + 1) * 32, plan.smem_bytes, stream>>>(map, p);
+}
+
+template <int HALO>
+void fill_t(GradPlan& pl) {
+    using GEO = GGeomT<HALO>;
+    pl.halo_x = GEO::HX; pl.halo_y = GEO::HY;
+    pl.row_stride = GEO::ROW; pl.img_stride = 0;
+    pl.feat_stride = (GEO::FEAT_BYTES + 127) / 128 * 128 / 4;    // words
+}
+
+}  // namespace
+
+// ---- layouts -------------------------------------------------------------------------------------
+size_t strip_layout_floats(int N, int S, int H, int W) {
+    const size_t items = (size_t)N * ((H + TH - 1) / TH) * ((W + TW - 1) / TW);
+    return items * S * (XK_WARP_BYTES / 4);
+}
+size_t error_layout_floats(int N, int F, int H, int W) {
+    const size_t qv = (W + 1) / 2, qp = (qv + 3) / 4 * 4;
+    return (size_t)N * F * H * 2 * qp;
+}
+
+bool plan_grad_tma(int N, int S, int F, int G, int H, int W, int max_off, int num_sms, GradPlan* out) {
+    if (W <= 32) return false;
+    int hclass = 0;
+    while (kHalos[hclass] < max_off) ++hclass;
+    GradPlan pl; memset(&pl, 0, sizeof(pl));
+    pl.kind = 1; pl.variant = hclass;
+    pl.tile_w = TW; pl.tile_h = TH; pl.imgs = 1;
+    switch (hclass) {
+        case 0: fill_t<4>(pl); break;
+        case 1: fill_t<8>(pl); break;
+        case 2: fill_t<16>(pl); break;
+        default: fill_t<32>(pl); break;
+    }
+    const size_t budget = 200 * 1024 - 128, xk_bytes = (size_t)NW * XK_WARP_BYTES;
+    pl.g_chunk = G < UPW ? G : UPW;
+    int fc = UPW / pl.g_chunk;
+    if (fc > F) fc = F;
+    while (fc > 1 && 2 * ((size_t)fc * pl.feat_stride * 4 + xk_bytes) > budget) --fc;
+    if (2 * ((size_t)fc * pl.feat_stride * 4 + xk_bytes) > budget) return false;
+    pl.feats_per_cta = fc;
+    pl.units_per_warp = fc * pl.g_chunk;
+    const size_t stage = (size_t)fc * pl.feat_stride * 4 + xk_bytes;
+    pl.smem_bytes = 2 * stage + 128;
+    const long tx = (W + TW - 1) / TW, ty = (H + TH - 1) / TH;
+    const long items = tx * ty * N;
+    const int n_fchunks = (F + fc - 1) / fc, n_gchunks = (G + pl.g_chunk - 1) / pl.g_chunk;
+    pl.grid_x = n_fchunks * n_gchunks;
+    pl.grid_y = (S + NW - 1) / NW;
+    if (pl.grid_y > 65535) return false;
+    const long base = (long)pl.grid_x * pl.grid_y;
+    int best_split = 1; double best_eff = -1.0;
+    const int max_split = (int)(items < 64 ? items : 64);
+    for (int sp = 1; sp <= max_split; ++sp) {
+        const long per = (items + sp - 1) / sp;
+        const long waves = (base * sp + num_sms - 1) / num_sms;
+        const double eff = (double)(base * items) / ((double)waves * num_sms * per) - 0.002 * sp;
+        if (eff > best_eff + 1e-9) { best_eff = eff; best_split = sp; }
+    }
+    pl.n_splits = best_split; pl.grid_z = best_split;
+    pl.partial_floats = (size_t)best_split * 4 * S * G * F;
+    *out = pl;
+    return true;
+}
+
+void launch_grad_tma(const GradPlan& plan, const float* xk_strips, const float* err_sg, const UnitRec* table,
+                     float* partial, int N, int S, int F, int G, int H, int W, cudaStream_t stream) {
+    const uint64_t qv = (W + 1) / 2, qp = (qv + 3) / 4 * 4;
+    const uint64_t dims[4] = {qv, 2, (uint64_t)H, (uint64_t)N * F};
+    const uint64_t strides[3] = {qp * 4, 2 * qp * 4, (uint64_t)H * 2 * qp * 4};
+    const uint32_t box[4] = {(uint32_t)((TW + 2 * plan.halo_x) / 2), 2, (uint32_t)(TH + 2 * plan.halo_y), 1};
+    const CUtensorMap map = make_map_f32(err_sg, 4, dims, strides, box);
+    TGradParams p;
+    p.xs = xk_strips; p.table = table; p.partial = partial;
+    p.N = N; p.S = S; p.F = F; p.G = G;
+    p.FC = plan.feats_per_cta; p.GC = plan.g_chunk; p.n_gchunks = (G + p.GC - 1) / p.GC;
+    p.tiles_x = (W + TW - 1) / TW;
+    p.tiles = p.tiles_x * ((H + TH - 1) / TH);
+    p.items = p.tiles * N;
+    p.items_per_split = (p.items + plan.n_splits - 1) / plan.n_splits;
+    p.feat_bytes_al = plan.feat_stride * 4;
+    p.stage_bytes = (int)((plan.smem_bytes - 128) / 2);
+    switch (plan.variant) {
+        case 0: launch_t<4>(plan, map, p, stream); break;
+        case 1: launch_t<8>(plan, map, p, stream); break;
+        case 2: launch_t<16>(plan, map, p, stream); break;
+        default: launch_t<32>(plan, map, p, stream); break;
+    }
+    DAU_CUDA_CHECK(cudaGetLastError());
+}
+
+}  // namespace dau

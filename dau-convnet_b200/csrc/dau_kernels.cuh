@@ -78,6 +78,7 @@ void launch_blur_single_paired(const float* in, float* out_paired, int N, int Cn
 
 // ---- parameter gradients -----------------------------------------------------------------
 struct GradPlan {
+    int kind;                  // 0: cp.async kernel (dau_grad.cu); 1: TMA kernel (dau_grad_tma.cu)
     int variant;
     int tile_w, tile_h, imgs;
     int halo_x, halo_y;
@@ -95,6 +96,18 @@ GradPlan plan_grad(int N, int S, int F, int G, int H, int W, int max_off, int nu
 void launch_grad(const GradPlan& p, const float* xk, const float* err, const UnitRec* table,
                  float* partial, int N, int S, int F, int G, int H, int W,
                  int mask_last_row, int mask_last_col, cudaStream_t stream);
+
+// TMA variant: Xk in the strip-major layout (launch_blur_bank_strips), the error in the
+// de-interleaved layout SG[n][f][y][x%2][x/2] with the edge mask applied (launch_error_relayout)
+size_t strip_layout_floats(int N, int S, int H, int W);
+size_t error_layout_floats(int N, int F, int H, int W);
+bool plan_grad_tma(int N, int S, int F, int G, int H, int W, int max_off, int num_sms, GradPlan* out);
+void launch_grad_tma(const GradPlan& p, const float* xk_strips, const float* err_sg, const UnitRec* table,
+                     float* partial, int N, int S, int F, int G, int H, int W, cudaStream_t stream);
+void launch_blur_bank_strips(const float* in, float* out_strips, int N, int S, int H, int W,
+                             const BlurFactors& f, cudaStream_t stream);
+void launch_error_relayout(const float* err, float* out_sg, int planes, int H, int W, int mask_row, int mask_col,
+                           cudaStream_t stream);
 
 struct GradFinalizeArgs {
     const float* partial; int n_splits;

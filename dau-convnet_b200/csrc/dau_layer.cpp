@@ -63,7 +63,8 @@ void DAUConvLayerB200::Reshape(int N, int S, int H, int W, size_t* fwd_ws, size_
     // wide images: TMA + FFMA2 kernel on the paired gather layout; otherwise the cp.async kernel
     if (!plan_gather_tma(N, S, F_, G_, H, W, max_off_, &fwd_plan_)) fwd_plan_ = plan_gather(N, S, F_, G_, H, W, max_off_);
     if (!plan_gather_tma(N, F_, S, G_, H, W, max_off_, &bwd_plan_)) bwd_plan_ = plan_gather(N, F_, S, G_, H, W, max_off_);
-    grad_plan_ = plan_grad(N, S, F_, G_, H, W, max_off_, num_sms_);
+    if (!plan_grad_tma(N, S, F_, G_, H, W, max_off_, num_sms_, &grad_plan_))
+        grad_plan_ = plan_grad(N, S, F_, G_, H, W, max_off_, num_sms_);
     // forward workspace: blurred input | unit table | flag
     size_t o = 0;
     const size_t blur_in = fwd_plan_.kind == 1 ? paired_layout_floats(N, S, H, W) : act_in;
@@ -74,7 +75,10 @@ void DAUConvLayerB200::Reshape(int N, int S, int H, int W, size_t* fwd_ws, size_
     fwd_ws_ = o;
     // backward workspace: 4 derivative blurs | blurred error | two unit tables | split partials | flag
     o = 0;
-    off_bwd_xk_ = o;      o = align_up(o + 4 * act_in * sizeof(float));
+    const size_t xk_floats = grad_plan_.kind == 1 ? strip_layout_floats(N, S, H, W) : 4 * act_in;
+    const size_t esg_floats = grad_plan_.kind == 1 ? error_layout_floats(N, F_, H, W) : 0;
+    off_bwd_xk_ = o;      o = align_up(o + xk_floats * sizeof(float));
+    off_bwd_esg_ = o;     o = align_up(o + esg_floats * sizeof(float));
     off_bwd_eb_ = o;      o = align_up(o + blur_out * sizeof(float));
     off_bwd_table_ = o;   o = align_up(o + units * sizeof(UnitRec));
     off_bwd_gtable_ = o;  o = align_up(o + units * sizeof(UnitRec));
@@ -208,6 +212,7 @@ void DAUConvLayerB200::Backward_gpu(const float* bottom, const float* top_error,
     char* base = static_cast<char*>(ws);
     float* xk = reinterpret_cast<float*>(base + off_bwd_xk_);
     float* eb = reinterpret_cast<float*>(base + off_bwd_eb_);
+    float* esg = reinterpret_cast<float*>(base + off_bwd_esg_);
     UnitRec* btable = reinterpret_cast<UnitRec*>(base + off_bwd_table_);
     UnitRec* gtable = reinterpret_cast<UnitRec*>(base + off_bwd_gtable_);
     float* partial = reinterpret_cast<float*>(base + off_bwd_partial_);
@@ -225,7 +230,8 @@ void DAUConvLayerB200::Backward_gpu(const float* bottom, const float* top_error,
 
     if (want_params) {
         tic(1, 0, stream);
-        launch_blur_bank(bottom, xk, N_ * S_, H_, W_, f, stream);
+        if (grad_plan_.kind == 1) launch_blur_bank_strips(bottom, xk, N_, S_, H_, W_, f, stream);
+        else launch_blur_bank(bottom, xk, N_ * S_, H_, W_, f, stream);
         toc(1, 0, stream);
     }
     {
@@ -240,7 +246,12 @@ void DAUConvLayerB200::Backward_gpu(const float* bottom, const float* top_error,
         tic(1, 2, stream);
         const int mrow = st_.ignore_edge_gradients && edge_rule(H_) ? 1 : 0;
         const int mcol = st_.ignore_edge_gradients && edge_rule(W_) ? 1 : 0;
-        launch_grad(grad_plan_, xk, top_error, gtable, partial, N_, S_, F_, G_, H_, W_, mrow, mcol, stream);
+        if (grad_plan_.kind == 1) {
+            launch_error_relayout(top_error, esg, N_ * F_, H_, W_, mrow, mcol, stream);
+            launch_grad_tma(grad_plan_, xk, esg, gtable, partial, N_, S_, F_, G_, H_, W_, stream);
+        } else {
+            launch_grad(grad_plan_, xk, top_error, gtable, partial, N_, S_, F_, G_, H_, W_, mrow, mcol, stream);
+        }
         toc(1, 2, stream);
         tic(1, 3, stream);
         GradFinalizeArgs fa;
