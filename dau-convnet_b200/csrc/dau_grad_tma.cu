@@ -15,8 +15,16 @@
 //    the consumer warps execute no global loads and meet no CTA barrier.
 //
 // lane strip = 8 rows x 2 columns (16 pixels): 27 LDS per 128 FMA per unit.
+//
+// The math is packed fma.rn.f32x2 (SASS FFMA2): the two columns of the strip form the pair.
+//   e2      = {e(r,c0), e(r,c1)}        4 FFMA2 from the window pairs {p0,p1}, {p1,p2} of two rows
+//   acc2[k] += e2 * {xk(r,c0), xk(r,c1)}  4 FFMA2, column partial sums added at the very end
+// A scalar FFMA with three changing source registers issues at half rate on sm_100a
+// (tools/probes/fma_probe.cu), so the packed form is what reaches the FMA pipe's peak.
 #include "dau_geom.cuh"
 #include "dau_tma.cuh"
+
+#include <cstdlib>
 
 namespace dau {
 
@@ -24,7 +32,11 @@ namespace {
 
 using namespace tma;
 
-constexpr int R = 8, C = 2, NW = 8, UPW = 16, TW = 64, TH = 8;
+constexpr int R = 8, C = 2, NW = 8, UPW = 12, TW = 64, TH = 8;
+// CTA = 3 warpgroups: warpgroup 0 holds the producer lane and gives its registers away
+// (setmaxnreg.dec), warpgroups 1-2 are the 8 consumer warps and grow to CONS_REGS each
+// (setmaxnreg.inc): every SM sub-partition then holds 1 x PROD_REGS + 2 x CONS_REGS <= 512 per lane.
+constexpr int NTHREADS = (NW + 4) * 32, PROD_REGS = 40, CONS_REGS = 232;
 constexpr int XK_WARP_BYTES = 4 * R * 32 * C * 4;      // 8 KB: [k][r][lane][c]
 
 template <int HALO>
@@ -37,6 +49,13 @@ struct GGeomT {
     static constexpr int FEAT_BYTES = THH * ROW * 4;
 };
 
+// CTA-local copy of a unit record with the four tap weights duplicated into FFMA2 operands
+struct __align__(16) GUnit {
+    float2 w00, w01, w10, w11;
+    int offx, offy, tile_off, pad;
+};
+static_assert(sizeof(GUnit) == 48, "GUnit must be 48 bytes");
+
 struct TGradParams {
     const float* xs; const UnitRec* table; float* partial;
     int N, S, F, G;
@@ -44,19 +63,21 @@ struct TGradParams {
     int tiles_x, tiles, items, items_per_split;
     int feat_bytes_al;     // FEAT_BYTES rounded up to 128
     int stage_bytes;
+    int debug;             // DAU_DEBUG bits (development): 2 skip error tiles, 4 skip Xk copy, 8 skip the math
 };
 
 template <int HALO>
-__global__ void __launch_bounds__((NW + 1) * 32, 1)
+__global__ void __launch_bounds__(NTHREADS, 1)
 dau_grad_tma_kernel(const __grid_constant__ CUtensorMap err_map, const TGradParams p) {
     using GEO = GGeomT<HALO>;
     constexpr int QS = GEO::QS, ROW = GEO::ROW;
     extern __shared__ unsigned char smem_dyn[];
     __shared__ uint64_t full_bar[2], empty_bar[2];
-    __shared__ UnitRec s_units[NW][UPW];
+    __shared__ GUnit s_units[NW][UPW];
     unsigned char* smem_raw = smem_dyn + ((128u - (smem_u32(smem_dyn) & 127u)) & 127u);
 
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int warp = (tid >> 5) - 4;                   // consumer warp 0..7; negative: producer warpgroup
     // f-chunks vary fastest across the grid: CTAs that run together share the Xk block in L2
     const int fchunk = blockIdx.x / p.n_gchunks, gchunk = blockIdx.x - fchunk * p.n_gchunks;
     const int s0 = blockIdx.y * NW;
@@ -72,18 +93,29 @@ dau_grad_tma_kernel(const __grid_constant__ CUtensorMap err_map, const TGradPara
         for (int s = 0; s < 2; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], NW); }
         fence_barrier_init();
     }
-    if (warp < NW && s0 + warp < p.S && lane < nunits) {
-        const int fi = lane / ngc, gi = lane - fi * ngc;
-        UnitRec r = p.table[((size_t)(s0 + warp) * F + f0 + fi) * G + g0 + gi];
-        r.pad0 = fi * (p.feat_bytes_al / 4);           // word offset of the feature's error tile
-        s_units[warp][lane] = r;
+    if (warp >= 0 && lane < UPW) {
+        // slots beyond the chunk's units are dummies (zero weights, in-tile offsets): the unit loop
+        // below is branch-free so that one unit's prologue overlaps the previous unit's math
+        GUnit gu;
+        gu.w00 = gu.w01 = gu.w10 = gu.w11 = make_float2(0.f, 0.f);
+        gu.offx = GEO::HX; gu.offy = GEO::HY; gu.tile_off = 0; gu.pad = 0;
+        if (s0 + warp < p.S && lane < nunits) {
+            const int fi = lane / ngc, gi = lane - fi * ngc;
+            const UnitRec r = p.table[((size_t)(s0 + warp) * F + f0 + fi) * G + g0 + gi];
+            gu.w00 = make_float2(r.w00, r.w00); gu.w01 = make_float2(r.w01, r.w01);
+            gu.w10 = make_float2(r.w10, r.w10); gu.w11 = make_float2(r.w11, r.w11);
+            gu.offx = r.offx_h; gu.offy = r.offy_h;
+            gu.tile_off = fi * (p.feat_bytes_al / 4);  // word offset of the feature's error tile
+        }
+        s_units[warp][lane] = gu;
     }
     __syncthreads();
 
-    if (warp == NW) {
-        if (lane == 0) {
+    if (warp < 0) {
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;\n" ::"n"(PROD_REGS));
+        if (warp == -4 && lane == 0) {
             prefetch_map(&err_map);
-            const uint32_t tx = nfeat * GEO::FEAT_BYTES + nsv * XK_WARP_BYTES;
+            const uint32_t tx = ((p.debug & 2) ? 0 : nfeat * GEO::FEAT_BYTES) + ((p.debug & 4) ? 0 : nsv * XK_WARP_BYTES);
             for (int item = item_begin; item < item_end; ++item) {
                 const int k = item - item_begin, st = k & 1, use = k >> 1;
                 if (use > 0) mbar_wait(&empty_bar[st], (use - 1) & 1);
@@ -91,10 +123,10 @@ dau_grad_tma_kernel(const __grid_constant__ CUtensorMap err_map, const TGradPara
                 const int tyi = t / p.tiles_x, txi = t - tyi * p.tiles_x;
                 unsigned char* dst = smem_raw + (size_t)st * p.stage_bytes;
                 mbar_arrive_expect_tx(&full_bar[st], tx);
-                for (int fi = 0; fi < nfeat; ++fi)
+                for (int fi = 0; fi < nfeat && !(p.debug & 2); ++fi)
                     tensor4_g2s(dst + fi * p.feat_bytes_al, &err_map, (txi * TW - GEO::HX) / 2, 0,
                                 tyi * TH - GEO::HY, n * F + f0 + fi, &full_bar[st]);
-                bulk_g2s(dst + p.FC * p.feat_bytes_al,
+                if (!(p.debug & 4)) bulk_g2s(dst + p.FC * p.feat_bytes_al,
                          p.xs + ((size_t)item * p.S + s0) * (XK_WARP_BYTES / 4), nsv * XK_WARP_BYTES, &full_bar[st]);
             }
         }
@@ -102,18 +134,19 @@ dau_grad_tma_kernel(const __grid_constant__ CUtensorMap err_map, const TGradPara
     }
 
     // ---- consumer warps: warp = input channel s0 + warp -------------------------------------------
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;\n" ::"n"(CONS_REGS));
     const bool s_valid = warp < nsv;
-    float acc[UPW][4];
+    float2 acc[UPW][4];                                // {column 0, column 1} partial sums
 #pragma unroll
     for (int u = 0; u < UPW; ++u)
 #pragma unroll
-        for (int k = 0; k < 4; ++k) acc[u][k] = 0.f;
+        for (int k = 0; k < 4; ++k) acc[u][k] = make_float2(0.f, 0.f);
 
     for (int item = item_begin; item < item_end; ++item) {
         const int kk = item - item_begin, st = kk & 1, use = kk >> 1;
         mbar_wait(&full_bar[st], use & 1);
         const unsigned char* sbase = smem_raw + (size_t)st * p.stage_bytes;
-        if (s_valid) {
+        if (s_valid && !(p.debug & 8)) {
             float2 xk[4][R];
             const float2* xsrc = reinterpret_cast<const float2*>(sbase + p.FC * p.feat_bytes_al +
                                                                  warp * XK_WARP_BYTES) + lane;
@@ -124,10 +157,13 @@ dau_grad_tma_kernel(const __grid_constant__ CUtensorMap err_map, const TGradPara
             const float* tb = reinterpret_cast<const float*>(sbase) + lane;
 #pragma unroll
             for (int u = 0; u < UPW; ++u) {
-                if (u < nunits) {
-                    const UnitRec* rec = &s_units[warp][u];
-                    const float4 wv = *reinterpret_cast<const float4*>(rec);
-                    const int4 off = *reinterpret_cast<const int4*>(&rec->offx_h);   // offx, offy, tile offset
+                {
+                    const GUnit* rec = &s_units[warp][u];
+                    const float4 wa = *reinterpret_cast<const float4*>(&rec->w00);   // w00 w00 w01 w01
+                    const float4 wb = *reinterpret_cast<const float4*>(&rec->w10);   // w10 w10 w11 w11
+                    const int4 off = *reinterpret_cast<const int4*>(&rec->offx);     // offx, offy, tile offset
+                    const float2 w00 = make_float2(wa.x, wa.y), w01 = make_float2(wa.z, wa.w);
+                    const float2 w10 = make_float2(wb.x, wb.y), w11 = make_float2(wb.z, wb.w);
                     const int b = off.x & 1;
                     const float* base = tb + off.z + off.y * ROW + (off.x >> 1);
                     const float* colp[C + 1];
@@ -136,26 +172,22 @@ dau_grad_tma_kernel(const __grid_constant__ CUtensorMap err_map, const TGradPara
                         const int m = b + c;
                         colp[c] = base + (m & 1) * QS + (m >> 1);
                     }
-                    float prev[C + 1];
-#pragma unroll
-                    for (int c = 0; c <= C; ++c) prev[c] = colp[c][0];
+                    float2 pa, pb;                             // window row r: {p0,p1}, {p1,p2}
+                    {
+                        const float p0 = colp[0][0], p1 = colp[1][0], p2 = colp[2][0];
+                        pa = make_float2(p0, p1); pb = make_float2(p1, p2);
+                    }
 #pragma unroll
                     for (int r = 1; r <= R; ++r) {
-                        float cur[C + 1];
+                        const float q0 = colp[0][r * ROW], q1 = colp[1][r * ROW], q2 = colp[2][r * ROW];
+                        const float2 qa = make_float2(q0, q1), qb = make_float2(q1, q2);
+                        float2 e = __fmul2_rn(w00, pa);
+                        e = __ffma2_rn(w01, pb, e);
+                        e = __ffma2_rn(w10, qa, e);
+                        e = __ffma2_rn(w11, qb, e);
 #pragma unroll
-                        for (int c = 0; c <= C; ++c) cur[c] = colp[c][r * ROW];
-#pragma unroll
-                        for (int c = 0; c < C; ++c) {
-                            float e = wv.x * prev[c];
-                            e = fmaf(wv.y, prev[c + 1], e);
-                            e = fmaf(wv.z, cur[c], e);
-                            e = fmaf(wv.w, cur[c + 1], e);
-#pragma unroll
-                            for (int k = 0; k < 4; ++k)
-                                acc[u][k] = fmaf(e, c == 0 ? xk[k][r - 1].x : xk[k][r - 1].y, acc[u][k]);
-                        }
-#pragma unroll
-                        for (int c = 0; c <= C; ++c) prev[c] = cur[c];
+                        for (int k = 0; k < 4; ++k) acc[u][k] = __ffma2_rn(e, xk[k][r - 1], acc[u][k]);
+                        pa = qa; pb = qb;
                     }
                 }
             }
@@ -175,7 +207,7 @@ dau_grad_tma_kernel(const __grid_constant__ CUtensorMap err_map, const TGradPara
                 const size_t idx = ((size_t)s * G + g0 + gi) * F + f0 + fi;
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
-                    float v = acc[u][k];
+                    float v = acc[u][k].x + acc[u][k].y;
 #pragma unroll
                     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
                     if (lane == 0) pbase[(size_t)k * sgf + idx] = v;
@@ -196,7 +228,7 @@ void launch_t(const GradPlan& plan, const CUtensorMap& map, const TGradParams& p
         attr_set = true;
     }
     dim3 grid(plan.grid_x, plan.grid_y, plan.grid_z);
-    dau_grad_tma_kernel<HALO><<<grid, (NW + 1) * 32, plan.smem_bytes, stream>>>(map, p);
+    dau_grad_tma_kernel<HALO><<<grid, NTHREADS, plan.smem_bytes, stream>>>(map, p);
 }
 
 template <int HALO>
@@ -280,6 +312,7 @@ void launch_grad_tma(const GradPlan& plan, const float* xk_strips, const float* 
     p.items_per_split = (p.items + plan.n_splits - 1) / plan.n_splits;
     p.feat_bytes_al = plan.feat_stride * 4;
     p.stage_bytes = (int)((plan.smem_bytes - 128) / 2);
+    p.debug = getenv("DAU_DEBUG") ? atoi(getenv("DAU_DEBUG")) : 0;
     switch (plan.variant) {
         case 0: launch_t<4>(plan, map, p, stream); break;
         case 1: launch_t<8>(plan, map, p, stream); break;
