@@ -1,26 +1,30 @@
-// Per-unit parameter gradients, TMA variant for sm_100a (images wider than 32 px).
+// Per-unit parameter gradients, TMA + packed-FFMA2 variant for sm_100a (images wider than 32 px).
 // Same math, operand roles and reference mapping as dau_grad.cu (Xk resident in registers,
-// the error gathered from a haloed shared-memory tile); what changes is how operands move:
+// the error gathered from a haloed shared-memory tile); what changes is how operands move and
+// how the FMAs are packed:
 //
+//  * work item = (image PAIR, 4-row x 64-column tile).  Everything is laid out so that the two
+//    images of a pair are the two halves of one fma.rn.f32x2 (SASS FFMA2) operand: they share the
+//    unit's offsets and bilinear weights, so no register shuffling is ever needed to form pairs;
 //  * the derivative-blur kernel writes Xk "strip-major":
-//        XS[item][s][k][r][lane][c],  item = (n, tile_y, tile_x), r < 8, c < 2
-//    so that everything the 8 warps (= 8 input channels) of a CTA need for one item is ONE
-//    contiguous 64 KB block fetched by ONE cp.async.bulk;
+//        XS[item][s][k][r<4][lane<32][c<2][img<2]
+//    so that everything the 8 consumer warps (= 8 input channels) of a CTA need for one item is
+//    ONE contiguous 64 KB block fetched by ONE cp.async.bulk, and a lane reads its (k,r) strip
+//    row with one LDS.128;
 //  * the top error is re-laid out once (edge mask applied) as
-//        SG[n][f][y][x%2][x/2]
-//    so that the haloed tile of one (image, feature) is one 4-D TMA box, already column
-//    de-interleaved; 32 lanes x 2 columns cover the 64-px tile, every LDS.32 of the window is a
-//    single conflict-free wavefront whatever the unit's offset;
-//  * a producer warp streams items through a 2-stage ring guarded by full/empty mbarriers;
-//    the consumer warps execute no global loads and meet no CTA barrier.
+//        SGP[n/2][f][y][x%2][x/2][n%2]
+//    so that the haloed tile of one (image pair, feature) is one 4-D TMA box, already column
+//    de-interleaved; 32 lanes x 2 columns cover the 64-px tile and every LDS.64 of the window is
+//    two conflict-free wavefronts whatever the unit's offset;
+//  * a producer lane streams items through a 2-stage ring guarded by full/empty mbarriers; the
+//    consumer warps execute no global loads and meet no CTA barrier.
 //
-// lane strip = 8 rows x 2 columns (16 pixels): 27 LDS per 128 FMA per unit.
-//
-// The math is packed fma.rn.f32x2 (SASS FFMA2): the two columns of the strip form the pair.
-//   e2      = {e(r,c0), e(r,c1)}        4 FFMA2 from the window pairs {p0,p1}, {p1,p2} of two rows
-//   acc2[k] += e2 * {xk(r,c0), xk(r,c1)}  4 FFMA2, column partial sums added at the very end
-// A scalar FFMA with three changing source registers issues at half rate on sm_100a
-// (tools/probes/fma_probe.cu), so the packed form is what reaches the FMA pipe's peak.
+// Per unit and lane (strip = 4 rows x 2 columns x 2 images): 15 LDS.64 feed 64 FFMA2
+//   e2(r,c)  = w00*P[r][c] + w01*P[r][c+1] + w10*P[r+1][c] + w11*P[r+1][c+1]     (pairs over images)
+//   acc2[k] += e2(r,c) * xk2[k][r][c]            (image partial sums added at the very end)
+// A scalar FFMA whose three source registers all change issues at ~0.6 / clk / sub-partition on
+// sm_100a and a packed one with two changing pairs at ~0.4 (= 0.8 FMA-equivalents), see
+// tools/probes/fma_probe.cu; the packed form also halves the issue slots the math needs.
 #include "dau_geom.cuh"
 #include "dau_tma.cuh"
 
@@ -32,21 +36,21 @@ namespace {
 
 using namespace tma;
 
-constexpr int R = 8, C = 2, NW = 8, UPW = 12, TW = 64, TH = 8;
+constexpr int R = 4, C = 2, NW = 8, UPW = 12, TW = 64, TH = 4;
 // CTA = 3 warpgroups: warpgroup 0 holds the producer lane and gives its registers away
 // (setmaxnreg.dec), warpgroups 1-2 are the 8 consumer warps and grow to CONS_REGS each
 // (setmaxnreg.inc): every SM sub-partition then holds 1 x PROD_REGS + 2 x CONS_REGS <= 512 per lane.
 constexpr int NTHREADS = (NW + 4) * 32, PROD_REGS = 40, CONS_REGS = 232;
-constexpr int XK_WARP_BYTES = 4 * R * 32 * C * 4;      // 8 KB: [k][r][lane][c]
+constexpr int XK_WARP_BYTES = 4 * R * 32 * C * 2 * 4;  // 8 KB: [k][r][lane][c][img]
 
 template <int HALO>
 struct GGeomT {
-    // innermost TMA start coordinate (x0-HX)/2 floats must be a multiple of 4 floats
-    static constexpr int HX = (HALO + 7) / 8 * 8, HY = HALO;
-    static constexpr int QS = (TW + 2 * HX) / 2;       // words per column plane
+    // innermost TMA start coordinate (x0-HX) floats must be a multiple of 4 floats
+    static constexpr int HX = (HALO + 3) / 4 * 4, HY = HALO;
+    static constexpr int QS = (TW + 2 * HX) / 2;       // float2 per column plane
     static constexpr int THH = TH + 2 * HY;
-    static constexpr int ROW = 2 * QS;                 // words per tile row
-    static constexpr int FEAT_BYTES = THH * ROW * 4;
+    static constexpr int ROW = 2 * QS;                 // float2 per tile row
+    static constexpr int FEAT_BYTES = THH * ROW * 8;
 };
 
 // CTA-local copy of a unit record with the four tap weights duplicated into FFMA2 operands
@@ -105,7 +109,7 @@ dau_grad_tma_kernel(const __grid_constant__ CUtensorMap err_map, const TGradPara
             gu.w00 = make_float2(r.w00, r.w00); gu.w01 = make_float2(r.w01, r.w01);
             gu.w10 = make_float2(r.w10, r.w10); gu.w11 = make_float2(r.w11, r.w11);
             gu.offx = r.offx_h; gu.offy = r.offy_h;
-            gu.tile_off = fi * (p.feat_bytes_al / 4);  // word offset of the feature's error tile
+            gu.tile_off = fi * (p.feat_bytes_al / 8);  // float2 offset of the feature's error tile
         }
         s_units[warp][lane] = gu;
     }
@@ -119,12 +123,12 @@ dau_grad_tma_kernel(const __grid_constant__ CUtensorMap err_map, const TGradPara
             for (int item = item_begin; item < item_end; ++item) {
                 const int k = item - item_begin, st = k & 1, use = k >> 1;
                 if (use > 0) mbar_wait(&empty_bar[st], (use - 1) & 1);
-                const int n = item / p.tiles, t = item - n * p.tiles;
+                const int n = item / p.tiles, t = item - n * p.tiles;   // n = image pair
                 const int tyi = t / p.tiles_x, txi = t - tyi * p.tiles_x;
                 unsigned char* dst = smem_raw + (size_t)st * p.stage_bytes;
                 mbar_arrive_expect_tx(&full_bar[st], tx);
                 for (int fi = 0; fi < nfeat && !(p.debug & 2); ++fi)
-                    tensor4_g2s(dst + fi * p.feat_bytes_al, &err_map, (txi * TW - GEO::HX) / 2, 0,
+                    tensor4_g2s(dst + fi * p.feat_bytes_al, &err_map, txi * TW - GEO::HX, 0,
                                 tyi * TH - GEO::HY, n * F + f0 + fi, &full_bar[st]);
                 if (!(p.debug & 4)) bulk_g2s(dst + p.FC * p.feat_bytes_al,
                          p.xs + ((size_t)item * p.S + s0) * (XK_WARP_BYTES / 4), nsv * XK_WARP_BYTES, &full_bar[st]);
@@ -136,7 +140,7 @@ dau_grad_tma_kernel(const __grid_constant__ CUtensorMap err_map, const TGradPara
     // ---- consumer warps: warp = input channel s0 + warp -------------------------------------------
     asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;\n" ::"n"(CONS_REGS));
     const bool s_valid = warp < nsv;
-    float2 acc[UPW][4];                                // {column 0, column 1} partial sums
+    float2 acc[UPW][4];                                // {image 0, image 1} partial sums
 #pragma unroll
     for (int u = 0; u < UPW; ++u)
 #pragma unroll
@@ -147,48 +151,53 @@ dau_grad_tma_kernel(const __grid_constant__ CUtensorMap err_map, const TGradPara
         mbar_wait(&full_bar[st], use & 1);
         const unsigned char* sbase = smem_raw + (size_t)st * p.stage_bytes;
         if (s_valid && !(p.debug & 8)) {
-            float2 xk[4][R];
-            const float2* xsrc = reinterpret_cast<const float2*>(sbase + p.FC * p.feat_bytes_al +
+            float2 xk[4][R][C];
+            const float4* xsrc = reinterpret_cast<const float4*>(sbase + p.FC * p.feat_bytes_al +
                                                                  warp * XK_WARP_BYTES) + lane;
 #pragma unroll
             for (int k = 0; k < 4; ++k)
 #pragma unroll
-                for (int r = 0; r < R; ++r) xk[k][r] = xsrc[(k * R + r) * 32];
-            const float* tb = reinterpret_cast<const float*>(sbase) + lane;
+                for (int r = 0; r < R; ++r) {
+                    const float4 v = xsrc[(k * R + r) * 32];
+                    xk[k][r][0] = make_float2(v.x, v.y);
+                    xk[k][r][1] = make_float2(v.z, v.w);
+                }
+            const float2* tb = reinterpret_cast<const float2*>(sbase) + lane;
 #pragma unroll
             for (int u = 0; u < UPW; ++u) {
-                {
-                    const GUnit* rec = &s_units[warp][u];
-                    const float4 wa = *reinterpret_cast<const float4*>(&rec->w00);   // w00 w00 w01 w01
-                    const float4 wb = *reinterpret_cast<const float4*>(&rec->w10);   // w10 w10 w11 w11
-                    const int4 off = *reinterpret_cast<const int4*>(&rec->offx);     // offx, offy, tile offset
-                    const float2 w00 = make_float2(wa.x, wa.y), w01 = make_float2(wa.z, wa.w);
-                    const float2 w10 = make_float2(wb.x, wb.y), w11 = make_float2(wb.z, wb.w);
-                    const int b = off.x & 1;
-                    const float* base = tb + off.z + off.y * ROW + (off.x >> 1);
-                    const float* colp[C + 1];
+                const GUnit* rec = &s_units[warp][u];
+                const float4 wa = *reinterpret_cast<const float4*>(&rec->w00);   // w00 w00 w01 w01
+                const float4 wb = *reinterpret_cast<const float4*>(&rec->w10);   // w10 w10 w11 w11
+                const int4 off = *reinterpret_cast<const int4*>(&rec->offx);     // offx, offy, tile offset
+                const float2 w00 = make_float2(wa.x, wa.y), w01 = make_float2(wa.z, wa.w);
+                const float2 w10 = make_float2(wb.x, wb.y), w11 = make_float2(wb.z, wb.w);
+                const int b = off.x & 1;
+                const float2* base = tb + off.z + off.y * ROW + (off.x >> 1);
+                const float2* colp[C + 1];
 #pragma unroll
-                    for (int c = 0; c <= C; ++c) {
-                        const int m = b + c;
-                        colp[c] = base + (m & 1) * QS + (m >> 1);
-                    }
-                    float2 pa, pb;                             // window row r: {p0,p1}, {p1,p2}
-                    {
-                        const float p0 = colp[0][0], p1 = colp[1][0], p2 = colp[2][0];
-                        pa = make_float2(p0, p1); pb = make_float2(p1, p2);
+                for (int c = 0; c <= C; ++c) {
+                    const int m = b + c;
+                    colp[c] = base + (m & 1) * QS + (m >> 1);
+                }
+                float2 prev[C + 1];
+#pragma unroll
+                for (int c = 0; c <= C; ++c) prev[c] = colp[c][0];
+#pragma unroll
+                for (int r = 1; r <= R; ++r) {
+                    float2 cur[C + 1];
+#pragma unroll
+                    for (int c = 0; c <= C; ++c) cur[c] = colp[c][r * ROW];
+#pragma unroll
+                    for (int c = 0; c < C; ++c) {
+                        float2 e = __fmul2_rn(w00, prev[c]);
+                        e = __ffma2_rn(w01, prev[c + 1], e);
+                        e = __ffma2_rn(w10, cur[c], e);
+                        e = __ffma2_rn(w11, cur[c + 1], e);
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) acc[u][k] = __ffma2_rn(e, xk[k][r - 1][c], acc[u][k]);
                     }
 #pragma unroll
-                    for (int r = 1; r <= R; ++r) {
-                        const float q0 = colp[0][r * ROW], q1 = colp[1][r * ROW], q2 = colp[2][r * ROW];
-                        const float2 qa = make_float2(q0, q1), qb = make_float2(q1, q2);
-                        float2 e = __fmul2_rn(w00, pa);
-                        e = __ffma2_rn(w01, pb, e);
-                        e = __ffma2_rn(w10, qa, e);
-                        e = __ffma2_rn(w11, qb, e);
-#pragma unroll
-                        for (int k = 0; k < 4; ++k) acc[u][k] = __ffma2_rn(e, xk[k][r - 1], acc[u][k]);
-                        pa = qa; pb = qb;
-                    }
+                    for (int c = 0; c <= C; ++c) prev[c] = cur[c];
                 }
             }
         }
@@ -243,12 +252,12 @@ void fill_t(GradPlan& pl) {
 
 // ---- layouts -------------------------------------------------------------------------------------
 size_t strip_layout_floats(int N, int S, int H, int W) {
-    const size_t items = (size_t)N * ((H + TH - 1) / TH) * ((W + TW - 1) / TW);
+    const size_t items = (size_t)((N + 1) / 2) * ((H + TH - 1) / TH) * ((W + TW - 1) / TW);
     return items * S * (XK_WARP_BYTES / 4);
 }
 size_t error_layout_floats(int N, int F, int H, int W) {
-    const size_t qv = (W + 1) / 2, qp = (qv + 3) / 4 * 4;
-    return (size_t)N * F * H * 2 * qp;
+    const size_t qv = (W + 1) / 2, qp = (qv + 1) / 2 * 2;
+    return (size_t)((N + 1) / 2) * F * H * 2 * qp * 2;
 }
 
 bool plan_grad_tma(int N, int S, int F, int G, int H, int W, int max_off, int num_sms, GradPlan* out) {
@@ -257,7 +266,7 @@ bool plan_grad_tma(int N, int S, int F, int G, int H, int W, int max_off, int nu
     while (kHalos[hclass] < max_off) ++hclass;
     GradPlan pl; memset(&pl, 0, sizeof(pl));
     pl.kind = 1; pl.variant = hclass;
-    pl.tile_w = TW; pl.tile_h = TH; pl.imgs = 1;
+    pl.tile_w = TW; pl.tile_h = TH; pl.imgs = 2;
     switch (hclass) {
         case 0: fill_t<4>(pl); break;
         case 1: fill_t<8>(pl); break;
@@ -275,7 +284,7 @@ bool plan_grad_tma(int N, int S, int F, int G, int H, int W, int max_off, int nu
     const size_t stage = (size_t)fc * pl.feat_stride * 4 + xk_bytes;
     pl.smem_bytes = 2 * stage + 128;
     const long tx = (W + TW - 1) / TW, ty = (H + TH - 1) / TH;
-    const long items = tx * ty * N;
+    const long items = tx * ty * ((N + 1) / 2);
     const int n_fchunks = (F + fc - 1) / fc, n_gchunks = (G + pl.g_chunk - 1) / pl.g_chunk;
     pl.grid_x = n_fchunks * n_gchunks;
     pl.grid_y = (S + NW - 1) / NW;
@@ -297,10 +306,11 @@ bool plan_grad_tma(int N, int S, int F, int G, int H, int W, int max_off, int nu
 
 void launch_grad_tma(const GradPlan& plan, const float* xk_strips, const float* err_sg, const UnitRec* table,
                      float* partial, int N, int S, int F, int G, int H, int W, cudaStream_t stream) {
-    const uint64_t qv = (W + 1) / 2, qp = (qv + 3) / 4 * 4;
-    const uint64_t dims[4] = {qv, 2, (uint64_t)H, (uint64_t)N * F};
-    const uint64_t strides[3] = {qp * 4, 2 * qp * 4, (uint64_t)H * 2 * qp * 4};
-    const uint32_t box[4] = {(uint32_t)((TW + 2 * plan.halo_x) / 2), 2, (uint32_t)(TH + 2 * plan.halo_y), 1};
+    // tensor map of SGP[n/2][f][y][x%2][x/2][n%2]: dims (q*2+img, plane, y, (pair, f))
+    const uint64_t qv = (W + 1) / 2, qp = (qv + 1) / 2 * 2;
+    const uint64_t dims[4] = {2 * qv, 2, (uint64_t)H, (uint64_t)((N + 1) / 2) * F};
+    const uint64_t strides[3] = {qp * 8, 2 * qp * 8, (uint64_t)H * 2 * qp * 8};
+    const uint32_t box[4] = {(uint32_t)(TW + 2 * plan.halo_x), 2, (uint32_t)(TH + 2 * plan.halo_y), 1};
     const CUtensorMap map = make_map_f32(err_sg, 4, dims, strides, box);
     TGradParams p;
     p.xs = xk_strips; p.table = table; p.partial = partial;
@@ -308,7 +318,7 @@ void launch_grad_tma(const GradPlan& plan, const float* xk_strips, const float* 
     p.FC = plan.feats_per_cta; p.GC = plan.g_chunk; p.n_gchunks = (G + p.GC - 1) / p.GC;
     p.tiles_x = (W + TW - 1) / TW;
     p.tiles = p.tiles_x * ((H + TH - 1) / TH);
-    p.items = p.tiles * N;
+    p.items = p.tiles * ((N + 1) / 2);
     p.items_per_split = (p.items + plan.n_splits - 1) / plan.n_splits;
     p.feat_bytes_al = plan.feat_stride * 4;
     p.stage_bytes = (int)((plan.smem_bytes - 128) / 2);

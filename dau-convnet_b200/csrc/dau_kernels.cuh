@@ -97,8 +97,9 @@ void launch_grad(const GradPlan& p, const float* xk, const float* err, const Uni
                  float* partial, int N, int S, int F, int G, int H, int W,
                  int mask_last_row, int mask_last_col, cudaStream_t stream);
 
-// TMA variant: Xk in the strip-major layout (launch_blur_bank_strips), the error in the
-// de-interleaved layout SG[n][f][y][x%2][x/2] with the edge mask applied (launch_error_relayout)
+// TMA variant: Xk in the strip-major layout XS[item][s][k][r][lane][c][img] (launch_blur_bank_strips),
+// the error in the de-interleaved pair layout SGP[n/2][f][y][x%2][x/2][n%2] with the edge mask applied
+// (launch_error_relayout)
 size_t strip_layout_floats(int N, int S, int H, int W);
 size_t error_layout_floats(int N, int F, int H, int W);
 bool plan_grad_tma(int N, int S, int F, int G, int H, int W, int max_off, int num_sms, GradPlan* out);
@@ -106,7 +107,7 @@ void launch_grad_tma(const GradPlan& p, const float* xk_strips, const float* err
                      float* partial, int N, int S, int F, int G, int H, int W, cudaStream_t stream);
 void launch_blur_bank_strips(const float* in, float* out_strips, int N, int S, int H, int W,
                              const BlurFactors& f, cudaStream_t stream);
-void launch_error_relayout(const float* err, float* out_sg, int planes, int H, int W, int mask_row, int mask_col,
+void launch_error_relayout(const float* err, float* out_sg, int N, int F, int H, int W, int mask_row, int mask_col,
                            cudaStream_t stream);
 
 struct GradFinalizeArgs {

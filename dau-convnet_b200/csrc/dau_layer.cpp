@@ -247,7 +247,7 @@ void DAUConvLayerB200::Backward_gpu(const float* bottom, const float* top_error,
         const int mrow = st_.ignore_edge_gradients && edge_rule(H_) ? 1 : 0;
         const int mcol = st_.ignore_edge_gradients && edge_rule(W_) ? 1 : 0;
         if (grad_plan_.kind == 1) {
-            launch_error_relayout(top_error, esg, N_ * F_, H_, W_, mrow, mcol, stream);
+            launch_error_relayout(top_error, esg, N_, F_, H_, W_, mrow, mcol, stream);
             launch_grad_tma(grad_plan_, xk, esg, gtable, partial, N_, S_, F_, G_, H_, W_, stream);
         } else {
             launch_grad(grad_plan_, xk, top_error, gtable, partial, N_, S_, F_, G_, H_, W_, mrow, mcol, stream);

@@ -112,6 +112,58 @@ __global__ void __launch_bounds__(256) k_scalar_const(float* sink, int iters) {
     if (t == 123.456f) sink[0] = t;
 }
 
+// F/G: the gather kernel's pattern acc2[j] += w2[t] * v2[j]: weight pair warp-uniform.
+// F keeps the weights in the constant bank (ptxas: FFMA2 R, R, UR, R), G in vector registers.
+struct WPar { float2 w[8]; };
+__global__ void __launch_bounds__(256) k_packed_uniform_w(const __grid_constant__ WPar p, float* sink, int iters) {
+    float2 acc[16], v[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) { acc[j] = make_float2(threadIdx.x + j, j); v[j] = make_float2(1e-9f * j * threadIdx.x, 1e-9f * j); }
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int t = 0; t < 4; ++t)
+#pragma unroll
+            for (int j = 0; j < 16; ++j) acc[j] = __ffma2_rn(p.w[t], v[(j + t) & 15], acc[j]);
+    }
+    float t = 0.f;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) t += acc[j].x + acc[j].y;
+    if (t == 123.456f) sink[0] = t;
+}
+__global__ void __launch_bounds__(256) k_packed_vector_w(const float2* wsrc, float* sink, int iters) {
+    float2 acc[16], v[16], w[4];
+#pragma unroll
+    for (int t = 0; t < 4; ++t) w[t] = wsrc[t * 256 + threadIdx.x];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) { acc[j] = make_float2(threadIdx.x + j, j); v[j] = make_float2(1e-9f * j * threadIdx.x, 1e-9f * j); }
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int t = 0; t < 4; ++t)
+#pragma unroll
+            for (int j = 0; j < 16; ++j) acc[j] = __ffma2_rn(w[t], v[(j + t) & 15], acc[j]);
+    }
+    float t = 0.f;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) t += acc[j].x + acc[j].y;
+    if (t == 123.456f) sink[0] = t;
+}
+// H: scalar version of F (FFMA R, R, UR, R)
+__global__ void __launch_bounds__(256) k_scalar_uniform_w(const __grid_constant__ WPar p, float* sink, int iters) {
+    float acc[16], v[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) { acc[j] = threadIdx.x + j; v[j] = 1e-9f * j * threadIdx.x; }
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int t = 0; t < 4; ++t)
+#pragma unroll
+            for (int j = 0; j < 16; ++j) acc[j] = fmaf(p.w[t].x, v[(j + t) & 15], acc[j]);
+    }
+    float t = 0.f;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) t += acc[j];
+    if (t == 123.456f) sink[0] = t;
+}
+
 typedef void (*kern_t)(float*, int);
 
 int main() {
@@ -147,6 +199,29 @@ int main() {
             const double per_clk = inst / (ms * 1e-3 * clk_khz * 1e3) / (prop.multiProcessorCount * 4.0);
             printf("%s %8.3f ms  %6.2f TFLOP/s  %.3f warp-inst/clk/SMSP (at %d MHz nominal)\n", t.name, ms, tflops,
                    per_clk, clk_khz / 1000);
+        }
+    }
+    {
+        WPar wp; for (int t = 0; t < 8; ++t) wp.w[t] = make_float2(1.f + 1e-7f * t, 1.f - 1e-7f * t);
+        float2* wsrc; CK(cudaMalloc(&wsrc, 4 * 256 * sizeof(float2))); CK(cudaMemset(wsrc, 0, 4 * 256 * sizeof(float2)));
+        const int nb = prop.multiProcessorCount * 2, nthreads = 256;
+        for (int which = 0; which < 3; ++which) {
+            cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+            for (int rep = 0; rep < 2; ++rep) {
+                const int it = rep == 0 ? 100 : iters;
+                if (rep == 1) CK(cudaEventRecord(e0));
+                if (which == 0) k_packed_uniform_w<<<nb, nthreads>>>(wp, sink, it);
+                else if (which == 1) k_packed_vector_w<<<nb, nthreads>>>(wsrc, sink, it);
+                else k_scalar_uniform_w<<<nb, nthreads>>>(wp, sink, it);
+                if (rep == 1) CK(cudaEventRecord(e1));
+                CK(cudaDeviceSynchronize());
+            }
+            float ms; CK(cudaEventElapsedTime(&ms, e0, e1));
+            const double inst = (double)nb * (nthreads / 32) * iters * 64;
+            const int fpi = which == 2 ? 1 : 2;
+            printf("%s %8.3f ms  %6.2f TFLOP/s  %.3f warp-inst/clk/SMSP\n",
+                   which == 0 ? "FFMA2 acc+=w*v, w in uniform regs " : which == 1 ? "FFMA2 acc+=w*v, w in vector regs  " : "FFMA  acc+=w*v, w in uniform regs ",
+                   ms, inst * 32 * fpi * 2 / (ms * 1e-3) / 1e12, inst / (ms * 1e-3 * clk_khz * 1e3) / (prop.multiProcessorCount * 4.0));
         }
     }
     return 0;
