@@ -26,20 +26,17 @@ struct BlurArgsBank { float h[3][kMaxBlurTaps]; float v[3][kMaxBlurTaps]; };
 // MODE 0: one separable filter, one output plane per input plane.
 // MODE 1: derivative bank, four output planes [w, mu1, mu2, sigma] per input plane,
 //         laid out [plane][4][H][W] (the reference's [N*S, K, H, W], base_dau_conv_layer.cu:210-221).
-// MODE 2: one separable filter, output in the paired gather layout PG[n/2][c][y][x%4][x/4][n%2]
-//         consumed by dau_gather_tma.cu; planes >= N*Cn (the phantom image of an odd batch) and
-//         the pad columns x in [W, 4*ceil(W/4)) are written as zeros.
+// (The paired / strip-major layouts of the TMA kernels are written by dau_blur_pair.cu.)
 template <int MODE>
 __global__ void __launch_bounds__(256)
 blur_kernel(const float* __restrict__ in, float* __restrict__ out, int H, int W, int kb,
             const __grid_constant__ BlurArgs1 a1, const __grid_constant__ BlurArgsBank ab,
             int plane0, int N, int Cn, int tiles_x, int tiles_y) {
-    constexpr int NH = (MODE == 1 || MODE == 3) ? 3 : 1;
+    constexpr int NH = MODE == 1 ? 3 : 1;
     __shared__ float s_in[BIN][BIN + 1];
     __shared__ float s_h[NH][BIN][BT + 1];
     const int c = kb >> 1;
     const int plane = plane0 + blockIdx.z;
-    const bool phantom = (MODE == 2 || MODE == 3) && plane >= N * Cn;
     const int x0 = blockIdx.x * BT, y0 = blockIdx.y * BT;
     const float* src = in + (size_t)plane * H * W;
     const int tid = threadIdx.x;
@@ -49,7 +46,7 @@ blur_kernel(const float* __restrict__ in, float* __restrict__ out, int H, int W,
         const int r = i / span, q = i - r * span;
         const int gy = y0 + r - c, gx = x0 + q - c;
         float v = 0.f;
-        if (!phantom && gy >= 0 && gy < H && gx >= 0 && gx < W) v = __ldg(src + (size_t)gy * W + gx);
+        if (gy >= 0 && gy < H && gx >= 0 && gx < W) v = __ldg(src + (size_t)gy * W + gx);
         s_in[r][q] = v;
     }
     __syncthreads();
@@ -75,38 +72,6 @@ blur_kernel(const float* __restrict__ in, float* __restrict__ out, int H, int W,
     for (int i = tid; i < BT * BT; i += 256) {
         const int r = i / BT, q = i - r * BT;
         const int gy = y0 + r, gx = x0 + q;
-        if (MODE == 2) {
-            const int qv = (W + 3) >> 2, qp = (qv + 1) & ~1;
-            if (gy >= H || gx >= 4 * qv) continue;
-            float acc = 0.f;
-            if (gx < W)
-                for (int v = 0; v < kb; ++v) acc = fmaf(s_h[0][r + v][q], a1.fy[v], acc);
-            const int n = plane / Cn, cn = plane - n * Cn;
-            const size_t row = ((size_t)(n >> 1) * Cn + cn) * H + gy;
-            out[((row * 4 + (gx & 3)) * qp + (gx >> 2)) * 2 + (n & 1)] = acc;
-            continue;
-        }
-        if (MODE == 3) {
-            // derivative bank in the strip-major layout XS[item][s][k][r(4)][lane(32)][c(2)][img(2)] of
-            // dau_grad_tma.cu, item = (n/2, y/4, x/64); positions of the last tiles that fall outside
-            // the image and the phantom image of an odd batch are zeros
-            if (gy >= tiles_y * 4 || gx >= tiles_x * 64) continue;
-            float aw = 0.f, am1 = 0.f, am2 = 0.f, asg = 0.f;
-            if (!phantom && gy < H && gx < W)
-                for (int v = 0; v < kb; ++v) {
-                    const float t0 = s_h[0][r + v][q], t1 = s_h[1][r + v][q], t2 = s_h[2][r + v][q];
-                    aw = fmaf(t0, ab.v[0][v], aw);
-                    am1 = fmaf(t1, ab.v[0][v], am1);
-                    am2 = fmaf(t0, ab.v[1][v], am2);
-                    asg = fmaf(t2, ab.v[0][v], asg);
-                    asg = fmaf(t0, ab.v[2][v], asg);
-                }
-            const int n = plane / Cn, cn = plane - n * Cn;
-            const size_t item = ((size_t)(n >> 1) * tiles_y + (gy >> 2)) * tiles_x + (gx >> 6);
-            float* o = out + ((item * Cn + cn) * 16 + (gy & 3)) * 128 + (gx & 63) * 2 + (n & 1);
-            o[0] = aw; o[4 * 128] = am1; o[8 * 128] = am2; o[12 * 128] = asg;
-            continue;
-        }
         if (gy >= H || gx >= W) continue;
         if (MODE == 0) {
             float acc = 0.f;
@@ -148,20 +113,6 @@ void launch_blur_single(const float* in, float* out, int planes, int H, int W, i
     DAU_CUDA_CHECK(cudaGetLastError());
 }
 
-void launch_blur_single_paired(const float* in, float* out_paired, int N, int Cn, int H, int W, int kb,
-                               const float* fx, const float* fy, cudaStream_t stream) {
-    BlurArgs1 a1; BlurArgsBank ab;
-    memset(&a1, 0, sizeof(a1)); memset(&ab, 0, sizeof(ab));
-    for (int i = 0; i < kb; ++i) { a1.fx[i] = fx[i]; a1.fy[i] = fy[i]; }
-    const int planes = ((N + 1) / 2) * 2 * Cn;          // includes the phantom image of an odd batch
-    for (int p0 = 0; p0 < planes; p0 += 65535) {
-        const int np = planes - p0 < 65535 ? planes - p0 : 65535;
-        // `in` is indexed with the absolute plane number inside the kernel
-        blur_kernel<2><<<blur_grid(np, H, W), 256, 0, stream>>>(in, out_paired, H, W, kb, a1, ab, p0, N, Cn, 0, 0);
-    }
-    DAU_CUDA_CHECK(cudaGetLastError());
-}
-
 void launch_blur_bank(const float* in, float* out4, int planes, int H, int W,
                       const BlurFactors& f, cudaStream_t stream) {
     BlurArgs1 a1; BlurArgsBank ab;
@@ -174,24 +125,6 @@ void launch_blur_bank(const float* in, float* out4, int planes, int H, int W,
         const int np = planes - p0 < 65535 ? planes - p0 : 65535;
         blur_kernel<1><<<blur_grid(np, H, W), 256, 0, stream>>>(
             in + (size_t)p0 * H * W, out4 + (size_t)p0 * 4 * H * W, H, W, f.kb, a1, ab, 0, 0, 1, 0, 0);
-    }
-    DAU_CUDA_CHECK(cudaGetLastError());
-}
-
-void launch_blur_bank_strips(const float* in, float* out_strips, int N, int S, int H, int W,
-                             const BlurFactors& f, cudaStream_t stream) {
-    BlurArgs1 a1; BlurArgsBank ab;
-    memset(&a1, 0, sizeof(a1)); memset(&ab, 0, sizeof(ab));
-    for (int i = 0; i < f.kb; ++i) {
-        ab.h[0][i] = f.h0[i]; ab.h[1][i] = f.h1[i]; ab.h[2][i] = f.h2[i];
-        ab.v[0][i] = f.v0[i]; ab.v[1][i] = f.v1[i]; ab.v[2][i] = f.v2[i];
-    }
-    const int tx = (W + 63) / 64, ty = (H + 3) / 4;
-    const int planes = ((N + 1) / 2) * 2 * S;           // includes the phantom image of an odd batch
-    for (int p0 = 0; p0 < planes; p0 += 65535) {
-        const int np = planes - p0 < 65535 ? planes - p0 : 65535;
-        blur_kernel<3><<<blur_grid(np, ty * 4, tx * 64), 256, 0, stream>>>(in, out_strips, H, W, f.kb, a1, ab,
-                                                                            p0, N, S, tx, ty);
     }
     DAU_CUDA_CHECK(cudaGetLastError());
 }
