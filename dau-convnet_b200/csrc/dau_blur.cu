@@ -130,61 +130,44 @@ void launch_blur_bank(const float* in, float* out4, int planes, int H, int W,
 }
 
 namespace {
-// top error NCHW -> SGP[n/2][f][y][x%2][x/2][n%2] (row of x/2 padded to an even count), with the
-// ignore_edge_gradients mask (dau_conv_backward_core.hpp:2218-2222) applied on the way.  One thread
-// moves the column pair (2j, 2j+1) of both images: float2 loads, float2 stores, all coalesced.
+// top error NCHW -> SGP[n/2][f][y][x%2][x/2][n%2] of the MOSAIC image (row of x/2 padded to an even
+// count; gaps and cells beyond the batch are zeros), with the ignore_edge_gradients mask
+// (dau_conv_backward_core.hpp:2218-2222) applied on the way.  One thread moves the column pair
+// (2j, 2j+1) of both mosaic images of the pair; the float2 stores are coalesced.
 __global__ void __launch_bounds__(128) error_relayout_kernel(const float* __restrict__ err, float2* __restrict__ out,
-                                                             int N, int F, int H, int W, int qp,
+                                                             const __grid_constant__ Mosaic m, int F, int qp,
                                                              int mask_row, int mask_col) {
-    const int pf = blockIdx.y;                            // (pair, feature)
+    const int pf = blockIdx.x;                            // (pair, feature)
     const int np = pf / F, f = pf - np * F;
-    const int y = blockIdx.x;
-    const int n0 = 2 * np, n1 = 2 * np + 1;
-    const float* src0 = err + (((size_t)n0 * F + f) * H + y) * W;
-    const float* src1 = err + (((size_t)n1 * F + f) * H + y) * W;
-    float2* dst = out + ((size_t)pf * H + y) * 2 * qp;
-    const bool rowdead = mask_row && y == H - 1;
-    const bool has1 = n1 < N;
-    const bool vec = (W & 1) == 0;
+    const int vy = blockIdx.y;
+    float2* dst = out + ((size_t)pf * m.Hv + vy) * 2 * qp;
+    const size_t rplane = (size_t)m.H * m.W;
     for (int j = threadIdx.x; j < qp; j += 128) {
-        float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;     // a: column 2j, b: column 2j+1; 0/1: image
-        const int x = 2 * j;
-        if (!rowdead && x < W) {
-            if (vec) {
-                const float2 v0 = __ldg(reinterpret_cast<const float2*>(src0 + x));
-                a0 = v0.x; b0 = v0.y;
-                if (has1) { const float2 v1 = __ldg(reinterpret_cast<const float2*>(src1 + x)); a1 = v1.x; b1 = v1.y; }
-            } else {
-                a0 = __ldg(src0 + x);
-                if (x + 1 < W) b0 = __ldg(src0 + x + 1);
-                if (has1) { a1 = __ldg(src1 + x); if (x + 1 < W) b1 = __ldg(src1 + x + 1); }
+        float v[2][2] = {{0.f, 0.f}, {0.f, 0.f}};         // [column 2j / 2j+1][image of the pair]
+#pragma unroll
+        for (int c = 0; c < 2; ++c)
+#pragma unroll
+            for (int img = 0; img < 2; ++img) {
+                const int vx = 2 * j + c, nv = 2 * np + img;
+                int rn, ry, rx;
+                if (vx < m.Wv && nv < m.Nv && mosaic_to_real(m, nv, vy, vx, &rn, &ry, &rx)) {
+                    const bool dead = (mask_row && ry == m.H - 1) || (mask_col && rx == m.W - 1);
+                    if (!dead) v[c][img] = __ldg(err + ((size_t)rn * F + f) * rplane + (size_t)ry * m.W + rx);
+                }
             }
-            if (mask_col) {
-                if (x == W - 1) { a0 = 0.f; a1 = 0.f; }
-                if (x + 1 == W - 1) { b0 = 0.f; b1 = 0.f; }
-            }
-        }
-        dst[j] = make_float2(a0, a1);
-        dst[qp + j] = make_float2(b0, b1);
+        dst[j] = make_float2(v[0][0], v[0][1]);
+        dst[qp + j] = make_float2(v[1][0], v[1][1]);
     }
 }
 }  // namespace
 
-void launch_error_relayout(const float* err, float* out_sg, int N, int F, int H, int W, int mask_row, int mask_col,
+void launch_error_relayout(const float* err, float* out_sg, const Mosaic& m, int F, int mask_row, int mask_col,
                            cudaStream_t stream) {
-    const int qv = (W + 1) / 2, qp = (qv + 1) / 2 * 2;
-    const int pairs = (N + 1) / 2;
-    DAU_CHECK((long long)pairs * F <= 65535LL * 32768, 4, "batch x features too large for the error re-layout grid");
-    // gridDim.y limit: fold pairs*F over several launches
-    const long long total = (long long)pairs * F;
-    for (long long p0 = 0; p0 < total; p0 += 65535) {
-        const int np = (int)(total - p0 < 65535 ? total - p0 : 65535);
-        // feature/pair decoding inside the kernel needs the absolute index: shift the pointers only when
-        // p0 is a multiple of F (65535 is not in general), so pass the offset through blockIdx instead
-        DAU_CHECK(p0 == 0, 4, "batch x features above 65535 pairs is not supported by the error re-layout");
-        error_relayout_kernel<<<dim3(H, np), 128, 0, stream>>>(err, reinterpret_cast<float2*>(out_sg), N, F, H, W, qp,
-                                                               mask_row, mask_col);
-    }
+    const int qv = (m.Wv + 1) / 2, qp = (qv + 1) / 2 * 2;
+    const long long total = (long long)((m.Nv + 1) / 2) * F;
+    DAU_CHECK(total < (1LL << 31) && m.Hv <= 65535, 4, "shape too large for the error re-layout grid");
+    error_relayout_kernel<<<dim3((unsigned)total, m.Hv), 128, 0, stream>>>(err, reinterpret_cast<float2*>(out_sg), m, F, qp,
+                                                                           mask_row, mask_col);
     DAU_CUDA_CHECK(cudaGetLastError());
 }
 

@@ -24,13 +24,14 @@ constexpr int PT_MAXTAPS = 17;
 struct PairBlurArgs {
     float fx[3][PT_MAXTAPS];     // row filters, shifted: tap u' applies to tile column 4g + u' - 4*CQ
     float fy[3][PT_MAXTAPS];     // column filters, tap v applies to row y + v - c
-    int kb, H, W, N, Cn, z0;
+    int kb, H, W, N, Cn, z0;     // H, W, N: mosaic extents
+    Mosaic m;                    // mosaic <-> real image mapping (identity for wide images)
     int tiles_x, tiles_y;        // XS: 64-column / 4-row item grid
     int qp, qv;                  // PG: padded / valid float2-columns per plane
 };
 
 // MODE 2: one filter -> PG.   MODE 3: derivative bank (h0,h1,h2 / v0,v1,v2) -> XS.
-template <int MODE, int CQ>
+template <int MODE, int CQ, bool IDENT>
 __global__ void __launch_bounds__(PT_THREADS)
 blur_pair_kernel(const float* __restrict__ in, float* __restrict__ out, const __grid_constant__ PairBlurArgs a) {
     constexpr int NH = MODE == 3 ? 3 : 1, NOUT = MODE == 3 ? 4 : 1;
@@ -48,15 +49,24 @@ blur_pair_kernel(const float* __restrict__ in, float* __restrict__ out, const __
     float4 res[2][2][NOUT];
 #pragma unroll
     for (int img = 0; img < 2; ++img) {
-        const int n = 2 * np + img;
+        const int n = 2 * np + img;                          // mosaic image
         const bool live = n < a.N;
-        const float* src = in + ((size_t)n * a.Cn + cn) * H * W;
+        constexpr bool ident = IDENT;
+        const size_t rplane = (size_t)a.m.H * a.m.W;
         // ---- stage the haloed tile, zero outside the image --------------------------------------
         for (int i = tid; i < rows * SW; i += PT_THREADS) {
             const int r = i / SW, q = i - r * SW;
             const int gy = y0 + r - c, gx = x0 + q - PADX;
             float v = 0.f;
-            if (live && gy >= 0 && gy < H && gx >= 0 && gx < W) v = __ldg(src + (size_t)gy * W + gx);
+            if (live && gy >= 0 && gy < H && gx >= 0 && gx < W) {
+                if (ident) {
+                    v = __ldg(in + ((size_t)n * a.Cn + cn) * rplane + (size_t)gy * W + gx);
+                } else {
+                    int rn, ry, rx;
+                    if (mosaic_to_real(a.m, n, gy, gx, &rn, &ry, &rx))
+                        v = __ldg(in + ((size_t)rn * a.Cn + cn) * rplane + (size_t)ry * a.m.W + rx);
+                }
+            }
             s_in[i] = v;
         }
         __syncthreads();
@@ -118,12 +128,21 @@ blur_pair_kernel(const float* __restrict__ in, float* __restrict__ out, const __
             // zero what lies outside the image (pad columns / rows of the consumer layouts)
             const int gy = y0 + y, gx = x0 + 4 * g;
             const bool rowok = live && gy < H;
+            bool ok[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                ok[i] = rowok && gx + i < W;
+                if (ok[i] && !ident) {                       // blur tails inside the gaps are not image
+                    int rn, ry, rx;
+                    ok[i] = mosaic_to_real(a.m, n, gy, gx + i, &rn, &ry, &rx);
+                }
+            }
 #pragma unroll
             for (int k = 0; k < NOUT; ++k) {
-                if (!rowok || gx >= W) o[k].x = 0.f;
-                if (!rowok || gx + 1 >= W) o[k].y = 0.f;
-                if (!rowok || gx + 2 >= W) o[k].z = 0.f;
-                if (!rowok || gx + 3 >= W) o[k].w = 0.f;
+                if (!ok[0]) o[k].x = 0.f;
+                if (!ok[1]) o[k].y = 0.f;
+                if (!ok[2]) o[k].z = 0.f;
+                if (!ok[3]) o[k].w = 0.f;
                 res[img][tt][k] = o[k];
             }
         }
@@ -175,8 +194,10 @@ void launch_pair(const float* in, float* out, PairBlurArgs& a, int pairs_times_c
     const size_t smem = (size_t)(rows * sw + nh * rows * PT_W) * sizeof(float);
     static bool attr_set = false;
     if (!attr_set) {
-        DAU_CUDA_CHECK(cudaFuncSetAttribute(blur_pair_kernel<MODE, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
-        DAU_CUDA_CHECK(cudaFuncSetAttribute(blur_pair_kernel<MODE, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+        DAU_CUDA_CHECK(cudaFuncSetAttribute(blur_pair_kernel<MODE, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+        DAU_CUDA_CHECK(cudaFuncSetAttribute(blur_pair_kernel<MODE, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+        DAU_CUDA_CHECK(cudaFuncSetAttribute(blur_pair_kernel<MODE, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+        DAU_CUDA_CHECK(cudaFuncSetAttribute(blur_pair_kernel<MODE, 2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
         attr_set = true;
     }
     const int gx = MODE == 3 ? a.tiles_x : (a.W + PT_W - 1) / PT_W;
@@ -184,26 +205,36 @@ void launch_pair(const float* in, float* out, PairBlurArgs& a, int pairs_times_c
     for (int z0 = 0; z0 < pairs_times_c; z0 += 65535) {
         const int nz = pairs_times_c - z0 < 65535 ? pairs_times_c - z0 : 65535;
         a.z0 = z0;
-        if (cq == 1) blur_pair_kernel<MODE, 1><<<dim3(gx, gy, nz), PT_THREADS, smem, stream>>>(in, out, a);
-        else blur_pair_kernel<MODE, 2><<<dim3(gx, gy, nz), PT_THREADS, smem, stream>>>(in, out, a);
+        const bool ident = a.m.kx == 1 && a.m.ky == 1;
+        const dim3 grid(gx, gy, nz);
+        if (cq == 1 && ident) blur_pair_kernel<MODE, 1, true><<<grid, PT_THREADS, smem, stream>>>(in, out, a);
+        else if (cq == 1) blur_pair_kernel<MODE, 1, false><<<grid, PT_THREADS, smem, stream>>>(in, out, a);
+        else if (ident) blur_pair_kernel<MODE, 2, true><<<grid, PT_THREADS, smem, stream>>>(in, out, a);
+        else blur_pair_kernel<MODE, 2, false><<<grid, PT_THREADS, smem, stream>>>(in, out, a);
     }
     DAU_CUDA_CHECK(cudaGetLastError());
 }
 }  // namespace
 
-void launch_blur_single_paired(const float* in, float* out_paired, int N, int Cn, int H, int W, int kb,
+void launch_blur_single_paired(const float* in, float* out_paired, const Mosaic& m, int Cn, int kb,
                                const float* fx, const float* fy, cudaStream_t stream) {
+    const int N = m.Nv, H = m.Hv, W = m.Wv;
+    DAU_CHECK(m.gap >= (kb >> 1) || (m.kx == 1 && m.ky == 1), 4,
+              "blur wider than the mosaic gap: call dau_set_sigma_hint before dau_reshape");
     DAU_CHECK(kb >= 1 && kb <= PT_MAXTAPS && (kb & 1), 1, "blur kernel size must be odd and <= 17");
     PairBlurArgs a; memset(&a, 0, sizeof(a));
     fill_row_filter(a.fx[0], fx, kb, cq_of(kb));
     for (int i = 0; i < kb; ++i) a.fy[0][i] = fy[i];
-    a.kb = kb; a.H = H; a.W = W; a.N = N; a.Cn = Cn;
+    a.kb = kb; a.H = H; a.W = W; a.N = N; a.Cn = Cn; a.m = m;
     a.qv = (W + 3) / 4; a.qp = (a.qv + 1) / 2 * 2;
     launch_pair<2>(in, out_paired, a, ((N + 1) / 2) * Cn, stream);
 }
 
-void launch_blur_bank_strips(const float* in, float* out_strips, int N, int S, int H, int W,
+void launch_blur_bank_strips(const float* in, float* out_strips, const Mosaic& m, int S,
                              const BlurFactors& f, cudaStream_t stream) {
+    const int N = m.Nv, H = m.Hv, W = m.Wv;
+    DAU_CHECK(m.gap >= (f.kb >> 1) || (m.kx == 1 && m.ky == 1), 4,
+              "blur wider than the mosaic gap: call dau_set_sigma_hint before dau_reshape");
     DAU_CHECK(f.kb >= 1 && f.kb <= PT_MAXTAPS && (f.kb & 1), 1, "blur kernel size must be odd and <= 17");
     PairBlurArgs a; memset(&a, 0, sizeof(a));
     const int cq = cq_of(f.kb);
@@ -211,7 +242,7 @@ void launch_blur_bank_strips(const float* in, float* out_strips, int N, int S, i
     fill_row_filter(a.fx[1], f.h1, f.kb, cq);
     fill_row_filter(a.fx[2], f.h2, f.kb, cq);
     for (int i = 0; i < f.kb; ++i) { a.fy[0][i] = f.v0[i]; a.fy[1][i] = f.v1[i]; a.fy[2][i] = f.v2[i]; }
-    a.kb = f.kb; a.H = H; a.W = W; a.N = N; a.Cn = S;
+    a.kb = f.kb; a.H = H; a.W = W; a.N = N; a.Cn = S; a.m = m;
     a.tiles_x = (W + 63) / 64; a.tiles_y = (H + 3) / 4;
     launch_pair<3>(in, out_strips, a, ((N + 1) / 2) * S, stream);
 }

@@ -47,6 +47,7 @@ struct TGatherParams {
     int tiles_x, nstage;
     int stage_bytes;       // tile + records, multiple of 128
     int debug;
+    Mosaic m;              // N, H, W above are the mosaic extents; `out` is the real NCHW tensor
 };
 
 template <int HALO>
@@ -153,12 +154,13 @@ dau_gather_tma_kernel(const __grid_constant__ CUtensorMap in_map, const TGatherP
     const float bv = p.bias ? __ldg(p.bias + co) : 0.f;
     const int xs = x0 + lx * C;
     const int H = p.H, W = p.W;
-    const bool vec = ((W & 3) == 0) && (xs + C <= W);
+    const bool ident = p.m.kx == 1 && p.m.ky == 1;
+    const bool vec = ident && ((W & 3) == 0) && (xs + C <= W);
+    const size_t rplane = (size_t)p.m.H * p.m.W;
 #pragma unroll
     for (int img = 0; img < 2; ++img) {
         const int n = 2 * np + img;
         if (n >= p.N) break;
-        float* obase = p.out + ((size_t)n * p.Cout + co) * (size_t)H * W;
 #pragma unroll
         for (int r = 0; r < R; ++r) {
             const int y = y0 + ly * R + r;
@@ -166,13 +168,23 @@ dau_gather_tma_kernel(const __grid_constant__ CUtensorMap in_map, const TGatherP
             float v[C];
 #pragma unroll
             for (int c = 0; c < C; ++c) v[c] = (img == 0 ? acc[r][c].x : acc[r][c].y) + bv;
-            float* orow = obase + (size_t)y * W;
-            if (vec) {
-                *reinterpret_cast<float4*>(orow + xs) = make_float4(v[0], v[1], v[2], v[3]);
-            } else {
+            if (ident) {
+                float* orow = p.out + ((size_t)n * p.Cout + co) * rplane + (size_t)y * W;
+                if (vec) {
+                    *reinterpret_cast<float4*>(orow + xs) = make_float4(v[0], v[1], v[2], v[3]);
+                } else {
 #pragma unroll
-                for (int c = 0; c < C; ++c)
-                    if (xs + c < W) orow[xs + c] = v[c];
+                    for (int c = 0; c < C; ++c)
+                        if (xs + c < W) orow[xs + c] = v[c];
+                }
+            } else {
+                // mosaic: gap pixels and cells beyond the batch are computed but never stored
+#pragma unroll
+                for (int c = 0; c < C; ++c) {
+                    int rn, ry, rx;
+                    if (xs + c < W && mosaic_to_real(p.m, n, y, xs + c, &rn, &ry, &rx))
+                        p.out[((size_t)rn * p.Cout + co) * rplane + (size_t)ry * p.m.W + rx] = v[c];
+                }
             }
         }
     }
@@ -208,7 +220,6 @@ size_t paired_layout_floats(int N, int Cn, int H, int W) {
 }
 
 bool plan_gather_tma(int N, int Cin, int Cout, int G, int H, int W, int max_off, GatherPlan* out) {
-    if (W <= 32) return false;                    // narrower images use the cp.async kernel (dau_gather.cu)
     int hclass = 0;
     while (kHalos[hclass] < max_off) ++hclass;
     GatherPlan pl; memset(&pl, 0, sizeof(pl));
@@ -238,7 +249,8 @@ bool plan_gather_tma(int N, int Cin, int Cout, int G, int H, int W, int max_off,
 }
 
 void launch_gather_tma(const GatherPlan& plan, const float* in_paired, const UnitRec* table, const float* bias,
-                       float* out, int N, int Cin, int Cout, int G, int H, int W, cudaStream_t stream) {
+                       float* out, const Mosaic& m, int Cin, int Cout, int G, cudaStream_t stream) {
+    const int N = m.Nv, H = m.Hv, W = m.Wv;
     // tensor map of the paired gather layout: dims (q*2+i, p, y, plane)
     const uint64_t qv = (W + 3) / 4, qp = (qv + 1) / 2 * 2;
     const uint64_t dims[4] = {2 * qv, 4, (uint64_t)H, (uint64_t)((N + 1) / 2) * Cin};
@@ -251,6 +263,7 @@ void launch_gather_tma(const GatherPlan& plan, const float* in_paired, const Uni
     p.N = N; p.Cin = Cin; p.Cout = Cout; p.G = G; p.H = H; p.W = W;
     p.tiles_x = (W + TW - 1) / TW; p.nstage = plan.nstage;
     p.stage_bytes = plan.stage_words * 4;
+    p.m = m;
     p.debug = getenv("DAU_DEBUG") ? atoi(getenv("DAU_DEBUG")) : 0;
     switch (plan.variant) {
         case 0: launch_t<4>(plan, map, p, stream); break;

@@ -76,7 +76,8 @@ dau_grad_tma_kernel(const __grid_constant__ CUtensorMap err_map, const TGradPara
     using GEO = GGeomT<HALO>;
     constexpr int QS = GEO::QS, ROW = GEO::ROW;
     extern __shared__ unsigned char smem_dyn[];
-    __shared__ uint64_t full_bar[2], empty_bar[2];
+    __shared__ uint64_t full_bar[2], empty_bar[2];      // error-tile ring
+    __shared__ uint64_t xfull_bar, xempty_bar;           // the single Xk buffer
     __shared__ GUnit s_units[NW][UPW];
     unsigned char* smem_raw = smem_dyn + ((128u - (smem_u32(smem_dyn) & 127u)) & 127u);
 
@@ -95,6 +96,7 @@ dau_grad_tma_kernel(const __grid_constant__ CUtensorMap err_map, const TGradPara
 
     if (tid == 0) {
         for (int s = 0; s < 2; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], NW); }
+        mbar_init(&xfull_bar, 1); mbar_init(&xempty_bar, NW);
         fence_barrier_init();
     }
     if (warp >= 0 && lane < UPW) {
@@ -119,19 +121,25 @@ dau_grad_tma_kernel(const __grid_constant__ CUtensorMap err_map, const TGradPara
         asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;\n" ::"n"(PROD_REGS));
         if (warp == -4 && lane == 0) {
             prefetch_map(&err_map);
-            const uint32_t tx = ((p.debug & 2) ? 0 : nfeat * GEO::FEAT_BYTES) + ((p.debug & 4) ? 0 : nsv * XK_WARP_BYTES);
+            // Error tiles go through a 2-stage ring.  Xk needs ONE buffer only: the consumers move it
+            // to registers at the start of an item, so the next item's 64 KB copy overlaps the math.
+            const uint32_t tx_e = (p.debug & 2) ? 0 : nfeat * GEO::FEAT_BYTES;
+            const uint32_t tx_x = (p.debug & 4) ? 0 : nsv * XK_WARP_BYTES;
+            unsigned char* xdst = smem_raw + 2 * (size_t)p.stage_bytes;
             for (int item = item_begin; item < item_end; ++item) {
                 const int k = item - item_begin, st = k & 1, use = k >> 1;
-                if (use > 0) mbar_wait(&empty_bar[st], (use - 1) & 1);
                 const int n = item / p.tiles, t = item - n * p.tiles;   // n = image pair
                 const int tyi = t / p.tiles_x, txi = t - tyi * p.tiles_x;
+                if (k > 0) mbar_wait(&xempty_bar, (k - 1) & 1);
+                mbar_arrive_expect_tx(&xfull_bar, tx_x);
+                if (!(p.debug & 4)) bulk_g2s(xdst, p.xs + ((size_t)item * p.S + s0) * (XK_WARP_BYTES / 4),
+                                             nsv * XK_WARP_BYTES, &xfull_bar);
+                if (use > 0) mbar_wait(&empty_bar[st], (use - 1) & 1);
                 unsigned char* dst = smem_raw + (size_t)st * p.stage_bytes;
-                mbar_arrive_expect_tx(&full_bar[st], tx);
+                mbar_arrive_expect_tx(&full_bar[st], tx_e);
                 for (int fi = 0; fi < nfeat && !(p.debug & 2); ++fi)
                     tensor4_g2s(dst + fi * p.feat_bytes_al, &err_map, txi * TW - GEO::HX, 0,
                                 tyi * TH - GEO::HY, n * F + f0 + fi, &full_bar[st]);
-                if (!(p.debug & 4)) bulk_g2s(dst + p.FC * p.feat_bytes_al,
-                         p.xs + ((size_t)item * p.S + s0) * (XK_WARP_BYTES / 4), nsv * XK_WARP_BYTES, &full_bar[st]);
             }
         }
         return;
@@ -148,11 +156,10 @@ dau_grad_tma_kernel(const __grid_constant__ CUtensorMap err_map, const TGradPara
 
     for (int item = item_begin; item < item_end; ++item) {
         const int kk = item - item_begin, st = kk & 1, use = kk >> 1;
-        mbar_wait(&full_bar[st], use & 1);
-        const unsigned char* sbase = smem_raw + (size_t)st * p.stage_bytes;
-        if (s_valid && !(p.debug & 8)) {
-            float2 xk[4][R][C];
-            const float4* xsrc = reinterpret_cast<const float4*>(sbase + p.FC * p.feat_bytes_al +
+        float2 xk[4][R][C];
+        mbar_wait(&xfull_bar, kk & 1);
+        if (s_valid) {
+            const float4* xsrc = reinterpret_cast<const float4*>(smem_raw + 2 * (size_t)p.stage_bytes +
                                                                  warp * XK_WARP_BYTES) + lane;
 #pragma unroll
             for (int k = 0; k < 4; ++k)
@@ -162,6 +169,12 @@ dau_grad_tma_kernel(const __grid_constant__ CUtensorMap err_map, const TGradPara
                     xk[k][r][0] = make_float2(v.x, v.y);
                     xk[k][r][1] = make_float2(v.z, v.w);
                 }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&xempty_bar);           // the buffer may be refilled while we compute
+        mbar_wait(&full_bar[st], use & 1);
+        const unsigned char* sbase = smem_raw + (size_t)st * p.stage_bytes;
+        if (s_valid && !(p.debug & 8)) {
             const float2* tb = reinterpret_cast<const float2*>(sbase) + lane;
 #pragma unroll
             for (int u = 0; u < UPW; ++u) {
@@ -233,7 +246,7 @@ void launch_t(const GradPlan& plan, const CUtensorMap& map, const TGradParams& p
     static bool attr_set = false;
     if (!attr_set) {
         DAU_CUDA_CHECK(cudaFuncSetAttribute(dau_grad_tma_kernel<HALO>,
-                                            cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+                                            cudaFuncAttributeMaxDynamicSharedMemorySize, 221 * 1024));
         attr_set = true;
     }
     dim3 grid(plan.grid_x, plan.grid_y, plan.grid_z);
@@ -261,7 +274,6 @@ size_t error_layout_floats(int N, int F, int H, int W) {
 }
 
 bool plan_grad_tma(int N, int S, int F, int G, int H, int W, int max_off, int num_sms, GradPlan* out) {
-    if (W <= 32) return false;
     int hclass = 0;
     while (kHalos[hclass] < max_off) ++hclass;
     GradPlan pl; memset(&pl, 0, sizeof(pl));
@@ -273,16 +285,16 @@ bool plan_grad_tma(int N, int S, int F, int G, int H, int W, int max_off, int nu
         case 2: fill_t<16>(pl); break;
         default: fill_t<32>(pl); break;
     }
-    const size_t budget = 200 * 1024 - 128, xk_bytes = (size_t)NW * XK_WARP_BYTES;
+    const size_t budget = 220 * 1024 - 128, xk_bytes = (size_t)NW * XK_WARP_BYTES;
     pl.g_chunk = G < UPW ? G : UPW;
     int fc = UPW / pl.g_chunk;
     if (fc > F) fc = F;
-    while (fc > 1 && 2 * ((size_t)fc * pl.feat_stride * 4 + xk_bytes) > budget) --fc;
-    if (2 * ((size_t)fc * pl.feat_stride * 4 + xk_bytes) > budget) return false;
+    while (fc > 1 && 2 * (size_t)fc * pl.feat_stride * 4 + xk_bytes > budget) --fc;
+    if (2 * (size_t)fc * pl.feat_stride * 4 + xk_bytes > budget) return false;
     pl.feats_per_cta = fc;
     pl.units_per_warp = fc * pl.g_chunk;
-    const size_t stage = (size_t)fc * pl.feat_stride * 4 + xk_bytes;
-    pl.smem_bytes = 2 * stage + 128;
+    const size_t stage = (size_t)fc * pl.feat_stride * 4;     // error tiles of one ring stage
+    pl.smem_bytes = 2 * stage + xk_bytes + 128;
     const long tx = (W + TW - 1) / TW, ty = (H + TH - 1) / TH;
     const long items = tx * ty * ((N + 1) / 2);
     const int n_fchunks = (F + fc - 1) / fc, n_gchunks = (G + pl.g_chunk - 1) / pl.g_chunk;
@@ -321,7 +333,7 @@ void launch_grad_tma(const GradPlan& plan, const float* xk_strips, const float* 
     p.items = p.tiles * ((N + 1) / 2);
     p.items_per_split = (p.items + plan.n_splits - 1) / plan.n_splits;
     p.feat_bytes_al = plan.feat_stride * 4;
-    p.stage_bytes = (int)((plan.smem_bytes - 128) / 2);
+    p.stage_bytes = plan.feats_per_cta * plan.feat_stride * 4;
     p.debug = getenv("DAU_DEBUG") ? atoi(getenv("DAU_DEBUG")) : 0;
     switch (plan.variant) {
         case 0: launch_t<4>(plan, map, p, stream); break;

@@ -42,6 +42,32 @@ void launch_unit_prep(const UnitPrepArgs& a, UnitRec* fwd, UnitRec* bwd, UnitRec
 void launch_clip_params(float* mu1, float* mu2, float* sigma, int n, float mu_lo, float mu_hi,
                         float sigma_lo, cudaStream_t stream);
 
+// ---- image mosaic -------------------------------------------------------------------------
+// The TMA kernels work on 64-pixel-wide tiles.  Narrow images (AlexNet's 27x27 / 13x13 maps, the
+// 28x28 stress layer) are therefore packed kx x ky to a "mosaic" image, separated by `gap` zero
+// pixels (gap >= the largest displacement and >= the blur half-width), so that neither the blur
+// nor a displaced gather of one image can reach its neighbour: the zero gap IS the zero padding
+// the reference applies around every image.  Only the layout producers (blur, error re-layout)
+// and the gather's store know about it; wide images use the identity mosaic (kx = ky = 1).
+struct Mosaic {
+    int kx, ky;          // real images per mosaic row / column
+    int px, py;          // pitch: image extent + gap
+    int W, H;            // real image extent
+    int Wv, Hv;          // mosaic extent = k * pitch - gap
+    int N, Nv;           // real images, mosaic images
+    int gap;
+};
+Mosaic plan_mosaic(int N, int H, int W, int gap);
+
+// mosaic pixel -> real pixel; false for gap pixels and for cells beyond the batch
+__host__ __device__ inline bool mosaic_to_real(const Mosaic& m, int nv, int vy, int vx, int* n, int* y, int* x) {
+    const int jy = vy / m.py, jx = vx / m.px;
+    const int ly = vy - jy * m.py, lx = vx - jx * m.px;
+    const int nr = (nv * m.ky + jy) * m.kx + jx;
+    *n = nr; *y = ly; *x = lx;
+    return ly < m.H && lx < m.W && jy < m.ky && jx < m.kx && nr < m.N;
+}
+
 // ---- blur ------------------------------------------------------------------------------
 void launch_blur_single(const float* in, float* out, int planes, int H, int W, int kb,
                         const float* fx, const float* fy, cudaStream_t stream);
@@ -69,11 +95,13 @@ void launch_gather(const GatherPlan& p, const float* in, const UnitRec* table, c
 
 // TMA variant: `in_paired` is the blurred input in the paired gather layout
 //   PG[n/2][c][y][x%4][x/4][n%2]   (x/4 padded to an even count; written by launch_blur_single_paired)
+// (N, H, W below are the MOSAIC extents m.Nv, m.Hv, m.Wv; `in` / `out` of the producers and of
+// the gather's store are the caller's real NCHW tensors)
 size_t paired_layout_floats(int N, int Cn, int H, int W);
 bool plan_gather_tma(int N, int Cin, int Cout, int G, int H, int W, int max_off, GatherPlan* out);
 void launch_gather_tma(const GatherPlan& p, const float* in_paired, const UnitRec* table, const float* bias,
-                       float* out, int N, int Cin, int Cout, int G, int H, int W, cudaStream_t stream);
-void launch_blur_single_paired(const float* in, float* out_paired, int N, int Cn, int H, int W, int kb,
+                       float* out, const Mosaic& m, int Cin, int Cout, int G, cudaStream_t stream);
+void launch_blur_single_paired(const float* in, float* out_paired, const Mosaic& m, int Cn, int kb,
                                const float* fx, const float* fy, cudaStream_t stream);
 
 // ---- parameter gradients -----------------------------------------------------------------
@@ -105,9 +133,9 @@ size_t error_layout_floats(int N, int F, int H, int W);
 bool plan_grad_tma(int N, int S, int F, int G, int H, int W, int max_off, int num_sms, GradPlan* out);
 void launch_grad_tma(const GradPlan& p, const float* xk_strips, const float* err_sg, const UnitRec* table,
                      float* partial, int N, int S, int F, int G, int H, int W, cudaStream_t stream);
-void launch_blur_bank_strips(const float* in, float* out_strips, int N, int S, int H, int W,
+void launch_blur_bank_strips(const float* in, float* out_strips, const Mosaic& m, int S,
                              const BlurFactors& f, cudaStream_t stream);
-void launch_error_relayout(const float* err, float* out_sg, int N, int F, int H, int W, int mask_row, int mask_col,
+void launch_error_relayout(const float* err, float* out_sg, const Mosaic& m, int F, int mask_row, int mask_col,
                            cudaStream_t stream);
 
 struct GradFinalizeArgs {

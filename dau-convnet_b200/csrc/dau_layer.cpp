@@ -7,6 +7,7 @@
 //             blur(E, rotated) -> gather with the transposed table  [-> bias]   (6-7 launches)
 #include "dau_layer.hpp"
 
+#include <algorithm>
 #include <cmath>
 #include <cstring>
 
@@ -25,6 +26,39 @@ bool edge_rule(int n) {
     return false;
 }
 
+}  // namespace
+
+// Packs narrow images kx x ky to mosaic images so that the 64 x 16 tiles of the TMA kernels are
+// mostly image and not padding; scores every (kx, ky) by the fraction of computed pixels that
+// are real ones (tiles are 64 wide; 16 rows for the gathers, 4 for the gradients) and by how
+// evenly the batch divides into pairs of mosaics.
+Mosaic plan_mosaic(int N, int H, int W, int gap) {
+    Mosaic best; memset(&best, 0, sizeof(best));
+    double best_score = -1.0;
+    for (int ky = 1; ky <= 16; ++ky) {
+        const int Hv = ky * (H + gap) - gap;
+        if (ky > 1 && Hv > 256) break;
+        for (int kx = 1; kx <= 16; ++kx) {
+            const int Wv = kx * (W + gap) - gap;
+            if (kx > 1 && Wv > 512) break;
+            const int cells = kx * ky;
+            if (cells > 1 && 2 * cells > N) continue;          // never pad the batch by more than a pair
+            const int Nv = (N + cells - 1) / cells, pairs = (Nv + 1) / 2;
+            const double ex = (double)kx * W / (64.0 * ((Wv + 63) / 64));
+            const double ey = (double)ky * H / (16.0 * ((Hv + 15) / 16));
+            const double eb = (double)N / ((double)pairs * 2 * cells);
+            const double score = ex * ey * eb - 1e-3 * cells;
+            if (score > best_score + 1e-12) {
+                best_score = score;
+                best.kx = kx; best.ky = ky; best.px = W + gap; best.py = H + gap;
+                best.W = W; best.H = H; best.Wv = Wv; best.Hv = Hv; best.N = N; best.Nv = Nv; best.gap = gap;
+            }
+        }
+    }
+    return best;
+}
+
+namespace {
 const char* kFwdNames[] = {"clip_params", "blur_input", "unit_table", "gather_forward"};
 const char* kBwdNames[] = {"blur_bank", "unit_tables", "grad_units", "grad_finalize",
                            "blur_error", "gather_backprop", "bias_grad"};
@@ -60,23 +94,28 @@ void DAUConvLayerB200::Reshape(int N, int S, int H, int W, size_t* fwd_ws, size_
     N_ = N; S_ = S; H_ = H; W_ = W;
     const size_t act_in = (size_t)N * S * H * W, act_out = (size_t)N * F_ * H * W;
     const size_t units = (size_t)S * G_ * F_;
-    // wide images: TMA + FFMA2 kernel on the paired gather layout; otherwise the cp.async kernel
-    if (!plan_gather_tma(N, S, F_, G_, H, W, max_off_, &fwd_plan_)) fwd_plan_ = plan_gather(N, S, F_, G_, H, W, max_off_);
-    if (!plan_gather_tma(N, F_, S, G_, H, W, max_off_, &bwd_plan_)) bwd_plan_ = plan_gather(N, F_, S, G_, H, W, max_off_);
-    if (!plan_grad_tma(N, S, F_, G_, H, W, max_off_, num_sms_, &grad_plan_))
+    // TMA + FFMA2 kernels on the (mosaic) pair layouts; the first-generation cp.async kernels only
+    // where a TMA plan does not fit (displacements of 32 px need more shared memory than an SM has)
+    const float sig = sigma_hint_ > 0.f ? sigma_hint_ : 0.5f;      // the op's default sigma (dau_conv.py:296-297)
+    const int gap = std::max(max_off_, blur_kernel_size(sig) / 2);
+    mosaic_ = plan_mosaic(N, H, W, gap);
+    const Mosaic& m = mosaic_;
+    if (!plan_gather_tma(m.Nv, S, F_, G_, m.Hv, m.Wv, max_off_, &fwd_plan_)) fwd_plan_ = plan_gather(N, S, F_, G_, H, W, max_off_);
+    if (!plan_gather_tma(m.Nv, F_, S, G_, m.Hv, m.Wv, max_off_, &bwd_plan_)) bwd_plan_ = plan_gather(N, F_, S, G_, H, W, max_off_);
+    if (!plan_grad_tma(m.Nv, S, F_, G_, m.Hv, m.Wv, max_off_, num_sms_, &grad_plan_))
         grad_plan_ = plan_grad(N, S, F_, G_, H, W, max_off_, num_sms_);
     // forward workspace: blurred input | unit table | flag
     size_t o = 0;
-    const size_t blur_in = fwd_plan_.kind == 1 ? paired_layout_floats(N, S, H, W) : act_in;
-    const size_t blur_out = bwd_plan_.kind == 1 ? paired_layout_floats(N, F_, H, W) : act_out;
+    const size_t blur_in = fwd_plan_.kind == 1 ? paired_layout_floats(m.Nv, S, m.Hv, m.Wv) : act_in;
+    const size_t blur_out = bwd_plan_.kind == 1 ? paired_layout_floats(m.Nv, F_, m.Hv, m.Wv) : act_out;
     off_fwd_blur_ = o;  o = align_up(o + blur_in * sizeof(float));
     off_fwd_table_ = o; o = align_up(o + units * sizeof(UnitRec));
     off_fwd_flag_ = o;  o = align_up(o + 256);
     fwd_ws_ = o;
     // backward workspace: 4 derivative blurs | blurred error | two unit tables | split partials | flag
     o = 0;
-    const size_t xk_floats = grad_plan_.kind == 1 ? strip_layout_floats(N, S, H, W) : 4 * act_in;
-    const size_t esg_floats = grad_plan_.kind == 1 ? error_layout_floats(N, F_, H, W) : 0;
+    const size_t xk_floats = grad_plan_.kind == 1 ? strip_layout_floats(m.Nv, S, m.Hv, m.Wv) : 4 * act_in;
+    const size_t esg_floats = grad_plan_.kind == 1 ? error_layout_floats(m.Nv, F_, m.Hv, m.Wv) : 0;
     off_bwd_xk_ = o;      o = align_up(o + xk_floats * sizeof(float));
     off_bwd_esg_ = o;     o = align_up(o + esg_floats * sizeof(float));
     off_bwd_eb_ = o;      o = align_up(o + blur_out * sizeof(float));
@@ -177,7 +216,7 @@ void DAUConvLayerB200::Forward_gpu(const float* bottom, float* w, float* mu1, fl
     const BlurFactors& f = factors_for(sigma, stream);
 
     tic(0, 1, stream);
-    if (fwd_plan_.kind == 1) launch_blur_single_paired(bottom, xb, N_, S_, H_, W_, f.kb, f.fwd_x, f.fwd_y, stream);
+    if (fwd_plan_.kind == 1) launch_blur_single_paired(bottom, xb, mosaic_, S_, f.kb, f.fwd_x, f.fwd_y, stream);
     else launch_blur_single(bottom, xb, N_ * S_, H_, W_, f.kb, f.fwd_x, f.fwd_y, stream);
     toc(0, 1, stream);
 
@@ -193,7 +232,7 @@ void DAUConvLayerB200::Forward_gpu(const float* bottom, float* w, float* mu1, fl
 
     tic(0, 3, stream);
     if (fwd_plan_.kind == 1)
-        launch_gather_tma(fwd_plan_, xb, table, st_.bias_term ? bias : nullptr, top, N_, S_, F_, G_, H_, W_, stream);
+        launch_gather_tma(fwd_plan_, xb, table, st_.bias_term ? bias : nullptr, top, mosaic_, S_, F_, G_, stream);
     else
         launch_gather(fwd_plan_, xb, table, st_.bias_term ? bias : nullptr, top, N_, S_, F_, G_, H_, W_, stream);
     toc(0, 3, stream);
@@ -230,7 +269,7 @@ void DAUConvLayerB200::Backward_gpu(const float* bottom, const float* top_error,
 
     if (want_params) {
         tic(1, 0, stream);
-        if (grad_plan_.kind == 1) launch_blur_bank_strips(bottom, xk, N_, S_, H_, W_, f, stream);
+        if (grad_plan_.kind == 1) launch_blur_bank_strips(bottom, xk, mosaic_, S_, f, stream);
         else launch_blur_bank(bottom, xk, N_ * S_, H_, W_, f, stream);
         toc(1, 0, stream);
     }
@@ -247,8 +286,8 @@ void DAUConvLayerB200::Backward_gpu(const float* bottom, const float* top_error,
         const int mrow = st_.ignore_edge_gradients && edge_rule(H_) ? 1 : 0;
         const int mcol = st_.ignore_edge_gradients && edge_rule(W_) ? 1 : 0;
         if (grad_plan_.kind == 1) {
-            launch_error_relayout(top_error, esg, N_, F_, H_, W_, mrow, mcol, stream);
-            launch_grad_tma(grad_plan_, xk, esg, gtable, partial, N_, S_, F_, G_, H_, W_, stream);
+            launch_error_relayout(top_error, esg, mosaic_, F_, mrow, mcol, stream);
+            launch_grad_tma(grad_plan_, xk, esg, gtable, partial, mosaic_.Nv, S_, F_, G_, mosaic_.Hv, mosaic_.Wv, stream);
         } else {
             launch_grad(grad_plan_, xk, top_error, gtable, partial, N_, S_, F_, G_, H_, W_, mrow, mcol, stream);
         }
@@ -269,12 +308,12 @@ void DAUConvLayerB200::Backward_gpu(const float* bottom, const float* top_error,
         // blur the error with the rotated filter, then gather with -mu and the parameters read
         // transposed (base_dau_conv_layer.cu:278-325)
         tic(1, 4, stream);
-        if (bwd_plan_.kind == 1) launch_blur_single_paired(top_error, eb, N_, F_, H_, W_, f.kb, f.err_x, f.err_y, stream);
+        if (bwd_plan_.kind == 1) launch_blur_single_paired(top_error, eb, mosaic_, F_, f.kb, f.err_x, f.err_y, stream);
         else launch_blur_single(top_error, eb, N_ * F_, H_, W_, f.kb, f.err_x, f.err_y, stream);
         toc(1, 4, stream);
         tic(1, 5, stream);
         if (bwd_plan_.kind == 1)
-            launch_gather_tma(bwd_plan_, eb, btable, nullptr, bottom_error, N_, F_, S_, G_, H_, W_, stream);
+            launch_gather_tma(bwd_plan_, eb, btable, nullptr, bottom_error, mosaic_, F_, S_, G_, stream);
         else
             launch_gather(bwd_plan_, eb, btable, nullptr, bottom_error, N_, F_, S_, G_, H_, W_, stream);
         toc(1, 5, stream);

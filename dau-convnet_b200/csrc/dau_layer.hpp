@@ -45,6 +45,7 @@ public:
     const dau_settings_t& settings() const { return st_; }
     const GatherPlan& fwd_plan() const { return fwd_plan_; }
     const GradPlan& grad_plan() const { return grad_plan_; }
+    const Mosaic& mosaic() const { return mosaic_; }
 
 private:
     const BlurFactors& factors_for(const float* sigma_dev, cudaStream_t stream);
@@ -57,6 +58,7 @@ private:
     bool shaped_ = false;
     GatherPlan fwd_plan_{}, bwd_plan_{};
     GradPlan grad_plan_{};
+    Mosaic mosaic_{};          // how narrow images are packed for the TMA kernels (identity when wide)
     size_t fwd_ws_ = 0, bwd_ws_ = 0;
     // workspace carving (byte offsets)
     size_t off_fwd_blur_ = 0, off_fwd_table_ = 0, off_fwd_flag_ = 0;
