@@ -163,6 +163,7 @@ def run_ours(args, rank, world, local_rank):
     sigma = torch.full_like(w, 0.5)
     h = dau_conv.get_handle(dev, num_output=F, number_units_x=units[0], number_units_y=units[1],
                             kernel_size=ks, pad=(ks - 1) // 2)
+    h.set_sigma_hint(0.5)                                        # sigma is fixed (dau_sigma_trainable=False)
     y = torch.empty((N, F, H, W), device=dev)
     flat = torch.zeros((4, 1, S, G, F), device=dev)              # one buffer: w, mu1, mu2, sigma grads
     grads = [flat[k] for k in range(4)]

@@ -1,7 +1,11 @@
-// Separable Gaussian / Gaussian-derivative blurs that feed the TMA kernels (images wider than
-// 32 px): same math and reference mapping as dau_blur.cu (caffe_gpu_convolve2,
-// src/dau_conv/util/convolve.cu:48-131, uses base_dau_conv_layer.cu:81-90, :210-221, :278-288),
-// built for HBM speed:
+// Separable Gaussian / Gaussian-derivative blurs of NCHW fp32 planes for sm_100a.
+//
+// Replaces caffe_gpu_convolve2 -> convolve2<...> of the reference (dense Kb x Kb "same"
+// correlation, filter in __constant__ memory, src/dau_conv/util/convolve.cu:48-131, index
+// algebra :107-124) in its three uses: forward blur (base_dau_conv_layer.cu:81-90), the 4
+// derivative blurs of the backward pass (:210-221) and the blur of the top error with the
+// rotated filter (:278-288).  out[y,x] = sum_{v,u} in[y+v-c, x+u-c] * fy[v]*fx[u], zero outside
+// the image.  Cost per pixel: (NH + NV)*Kb FMAs instead of NOUT*Kb^2.  Built for HBM speed:
 //
 //  * one CTA = one 64 x 32 output tile of one channel of an image PAIR: both images are filtered
 //    one after the other through the same shared-memory buffers and their results leave the SM

@@ -1,23 +1,38 @@
-// Displaced bilinear gather-accumulate, TMA + packed-FFMA2 variant for sm_100a (images wider
-// than 32 px).  Same math and reference mapping as dau_gather.cu; what changes is how operands
-// move:
+// Displaced bilinear gather-accumulate for sm_100a: the DAU forward pass and, with the
+// transposed / negated unit table, the error back-propagation dL/dx.
+//
+//   out[n,co,y,x] = sum_{ci,g} sum_{dy,dx in {0,1}} wt[ci,co,g][dy][dx] *
+//                   in0[n,ci, y + offy + dy, x + offx + dx]        (in0 = in, zero outside)
+//
+// Replaces DAUConv_forward_pipeline_kernel + interleave_input_data_kernel of the reference
+// (include/dau_conv/dau_conv_impl/dau_conv_forward_core.hpp:804-1605, :1607-1732) and their
+// dispatch ladder (src/dau_conv/dau_conv_impl/dau_conv_forward.cpp:129-264).  Differences by
+// design: no patch copy of the input in HBM, no atomics and no pre-zeroed output (one CTA owns
+// an output tile for ALL (ci,g) and stores it once), shapes are not restricted to F%16==0 /
+// even G.
 //
 //  * the producing blur kernel writes its output in the "paired gather layout"
-//        PG[n/2][c][y][x%4][x/4][n%2]
+//        PG[n/2][c][y][x%4][x/4][n%2]           (n = mosaic image, see Mosaic in dau_kernels.cuh)
 //    so that (a) a haloed tile of an image PAIR is one 4-D TMA box
 //    (cp.async.bulk.tensor, zero fill outside the image = the reference's zero padding of the
 //    blurred input, dau_conv_forward_core.hpp:1707-1710), landing in shared memory already
-//    column-de-interleaved, and (b) one LDS.64 fetches the same pixel of two images;
+//    column-de-interleaved, word(y, x) = y*ROW + (x % 4)*QS + x / 4, so the 5 window columns of
+//    16 lanes that sit 4 apart in x are consecutive float2 whatever the (data-dependent) offset
+//    is: every LDS.64 is two conflict-free wavefronts; and (b) one LDS.64 fetches the same
+//    pixel of two images;
 //  * a dedicated producer warp streams input channels through an NSTAGE ring of
 //    {tile, unit records} guarded by full/empty mbarriers; the 8 consumer warps never execute a
 //    load instruction for global memory and never meet at a CTA barrier;
+//  * unit = warp-uniform record {4 tap weights, integer offset}.  A lane reads the 9 x 5 window
+//    once and uses every word for up to 4 FMAs (both dx taps of two neighbouring columns, both
+//    dy taps of two neighbouring rows);
 //  * the math is fma.rn.f32x2 (FFMA2): both images of the pair share the unit's weights, so
 //    one instruction issues two FMAs -- the kernel is bound by shared-memory wavefronts
 //    (45 LDS.64 per 128 FFMA2 per lane), not by instruction issue.
 //
 // CTA = 8 consumer warps (8 output channels) + 1 producer warp; tile = 16 x 64 pixels x 2
 // images; lane = (lx 0..15, ly 0..1) owning an 8 x 4 strip of both images (64 accumulators).
-#include "dau_geom.cuh"
+#include "dau_kernels.cuh"
 #include "dau_tma.cuh"
 
 #include <cstdlib>

@@ -1,7 +1,26 @@
-// Per-unit parameter gradients, TMA + packed-FFMA2 variant for sm_100a (images wider than 32 px).
-// Same math, operand roles and reference mapping as dau_grad.cu (Xk resident in registers,
-// the error gathered from a haloed shared-memory tile); what changes is how operands move and
-// how the FMAs are packed:
+// Per-unit parameter gradients of the DAU layer for sm_100a (TMA + packed FFMA2).
+//
+//   R[k,s,g,f] = sum_{n,y,x} E[n,f,y,x] * sum_{dy,dx} b[dy][dx] * Xk[n,s, y+oy+dy, x+ox+dx]
+//   k in {w, mu1, mu2, sigma}: Xk = X blurred with the k-th derivative filter (zero outside).
+//
+// Replaces DAUConv_bwd_multi_pipeline_kernel + interleave_input_data_kernel +
+// interleave_error_data_kernel of the reference
+// (include/dau_conv/dau_conv_impl/dau_conv_backward_core.hpp:1017-1820, :2248-2380, :2118-2246)
+// and the K-grouping dispatch (src/dau_conv/dau_conv_impl/dau_conv_backward.cpp:173-320).
+//
+// Like the reference (:846-894, comment :2055-2057) the bilinear weights are moved onto the
+// error so the four k share one interpolation, but the roles of the two operands are swapped
+// with respect to it: substituting p' = p + o + tap,
+//   R[k,s,g,f] = sum_{n,p'} Xk[n,s,p'] * Ebar_{sgf}[n,p'],
+//   Ebar[p']   = sum_{dy,dx} b[dy][dx] * E0[n,f, p' - o - (dy,dx)]       (E0 zero outside)
+// so the operand that is read ONCE per (n,s,pixel) -- the four Xk values -- stays in
+// registers for all units of the pass, and the operand that is gathered at a data-dependent
+// displacement -- E -- comes from a haloed shared-memory tile where each word feeds up to
+// four FMAs.  Accumulators acc[unit][k] live in registers for the CTA's whole walk over its
+// items and are reduced across the warp once at the end -> one plain store per output into
+// partial[split]; no atomics, deterministic.
+//
+// How operands move and how the FMAs are packed:
 //
 //  * work item = (image PAIR, 4-row x 64-column tile).  Everything is laid out so that the two
 //    images of a pair are the two halves of one fma.rn.f32x2 (SASS FFMA2) operand: they share the
@@ -16,8 +35,10 @@
 //    so that the haloed tile of one (image pair, feature) is one 4-D TMA box, already column
 //    de-interleaved; 32 lanes x 2 columns cover the 64-px tile and every LDS.64 of the window is
 //    two conflict-free wavefronts whatever the unit's offset;
-//  * a producer lane streams items through a 2-stage ring guarded by full/empty mbarriers; the
-//    consumer warps execute no global loads and meet no CTA barrier.
+//  * a producer lane streams the error tiles of the items through a 2-stage ring and Xk through
+//    ONE buffer (the consumers move Xk to registers first thing, so the next item's copy
+//    overlaps the math), all guarded by full/empty mbarriers; the consumer warps execute no
+//    global loads and meet no CTA barrier.
 //
 // Per unit and lane (strip = 4 rows x 2 columns x 2 images): 15 LDS.64 feed 64 FFMA2
 //   e2(r,c)  = w00*P[r][c] + w01*P[r][c+1] + w10*P[r+1][c] + w11*P[r+1][c+1]     (pairs over images)
@@ -25,7 +46,7 @@
 // A scalar FFMA whose three source registers all change issues at ~0.6 / clk / sub-partition on
 // sm_100a and a packed one with two changing pairs at ~0.4 (= 0.8 FMA-equivalents), see
 // tools/probes/fma_probe.cu; the packed form also halves the issue slots the math needs.
-#include "dau_geom.cuh"
+#include "dau_kernels.cuh"
 #include "dau_tma.cuh"
 
 #include <cstdlib>

@@ -68,17 +68,10 @@ __host__ __device__ inline bool mosaic_to_real(const Mosaic& m, int nv, int vy, 
     return ly < m.H && lx < m.W && jy < m.ky && jx < m.kx && nr < m.N;
 }
 
-// ---- blur ------------------------------------------------------------------------------
-void launch_blur_single(const float* in, float* out, int planes, int H, int W, int kb,
-                        const float* fx, const float* fy, cudaStream_t stream);
-void launch_blur_bank(const float* in, float* out4, int planes, int H, int W,
-                      const BlurFactors& f, cudaStream_t stream);
-
 // ---- displaced gather (forward and dL/dx) -------------------------------------------------
-struct GatherPlan {            // chosen once per shape by plan_gather()
-    int kind;                  // 0: cp.async kernel on NCHW input (dau_gather.cu)
-                               // 1: TMA + FFMA2 kernel on the paired gather layout (dau_gather_tma.cu)
-    int nstage;                // pipeline depth (kind 1)
+struct GatherPlan {            // chosen once per shape by plan_gather_tma()
+    int kind;                  // 1: TMA + FFMA2 kernel on the paired gather layout (dau_gather_tma.cu)
+    int nstage;                // pipeline depth
     int variant;               // index into the instantiated tile shapes
     int tile_w, tile_h, imgs;  // output tile of one CTA: imgs x tile_h x tile_w
     int halo_x, halo_y;
@@ -88,10 +81,7 @@ struct GatherPlan {            // chosen once per shape by plan_gather()
     size_t smem_bytes;
     int grid_x, grid_y, grid_z;
 };
-GatherPlan plan_gather(int N, int Cin, int Cout, int G, int H, int W, int max_off);
 // out[n,co,y,x] = sum_{ci,g} gather(in[n,ci], table[ci][co][g]) (+ bias[co])
-void launch_gather(const GatherPlan& p, const float* in, const UnitRec* table, const float* bias,
-                   float* out, int N, int Cin, int Cout, int G, int H, int W, cudaStream_t stream);
 
 // TMA variant: `in_paired` is the blurred input in the paired gather layout
 //   PG[n/2][c][y][x%4][x/4][n%2]   (x/4 padded to an even count; written by launch_blur_single_paired)
@@ -106,7 +96,7 @@ void launch_blur_single_paired(const float* in, float* out_paired, const Mosaic&
 
 // ---- parameter gradients -----------------------------------------------------------------
 struct GradPlan {
-    int kind;                  // 0: cp.async kernel (dau_grad.cu); 1: TMA kernel (dau_grad_tma.cu)
+    int kind;                  // 1: TMA + FFMA2 kernel (dau_grad_tma.cu)
     int variant;
     int tile_w, tile_h, imgs;
     int halo_x, halo_y;
@@ -119,11 +109,7 @@ struct GradPlan {
     int grid_x, grid_y, grid_z;
     size_t partial_floats;     // n_splits * 4 * S*G*F
 };
-GradPlan plan_grad(int N, int S, int F, int G, int H, int W, int max_off, int num_sms);
 // partial[split][k][s][g][f] = sum over the split's (n,y,x) of  xk[n,s,k] * gather(err[n,f])
-void launch_grad(const GradPlan& p, const float* xk, const float* err, const UnitRec* table,
-                 float* partial, int N, int S, int F, int G, int H, int W,
-                 int mask_last_row, int mask_last_col, cudaStream_t stream);
 
 // TMA variant: Xk in the strip-major layout XS[item][s][k][r][lane][c][img] (launch_blur_bank_strips),
 // the error in the de-interleaved pair layout SGP[n/2][f][y][x%2][x/2][n%2] with the edge mask applied

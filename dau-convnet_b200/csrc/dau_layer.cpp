@@ -92,30 +92,27 @@ DAUConvLayerB200::~DAUConvLayerB200() {
 void DAUConvLayerB200::Reshape(int N, int S, int H, int W, size_t* fwd_ws, size_t* bwd_ws) {
     DAU_CHECK(N > 0 && S > 0 && H > 0 && W > 0, 1, "bottom shape must be a positive 4-D NCHW shape");
     N_ = N; S_ = S; H_ = H; W_ = W;
-    const size_t act_in = (size_t)N * S * H * W, act_out = (size_t)N * F_ * H * W;
     const size_t units = (size_t)S * G_ * F_;
-    // TMA + FFMA2 kernels on the (mosaic) pair layouts; the first-generation cp.async kernels only
-    // where a TMA plan does not fit (displacements of 32 px need more shared memory than an SM has)
+    // TMA + FFMA2 kernels on the (mosaic) pair layouts
     const float sig = sigma_hint_ > 0.f ? sigma_hint_ : 0.5f;      // the op's default sigma (dau_conv.py:296-297)
     const int gap = std::max(max_off_, blur_kernel_size(sig) / 2);
     mosaic_ = plan_mosaic(N, H, W, gap);
     const Mosaic& m = mosaic_;
-    if (!plan_gather_tma(m.Nv, S, F_, G_, m.Hv, m.Wv, max_off_, &fwd_plan_)) fwd_plan_ = plan_gather(N, S, F_, G_, H, W, max_off_);
-    if (!plan_gather_tma(m.Nv, F_, S, G_, m.Hv, m.Wv, max_off_, &bwd_plan_)) bwd_plan_ = plan_gather(N, F_, S, G_, H, W, max_off_);
-    if (!plan_grad_tma(m.Nv, S, F_, G_, m.Hv, m.Wv, max_off_, num_sms_, &grad_plan_))
-        grad_plan_ = plan_grad(N, S, F_, G_, H, W, max_off_, num_sms_);
+    DAU_CHECK(plan_gather_tma(m.Nv, S, F_, G_, m.Hv, m.Wv, max_off_, &fwd_plan_), 4, "no forward gather plan for this shape");
+    DAU_CHECK(plan_gather_tma(m.Nv, F_, S, G_, m.Hv, m.Wv, max_off_, &bwd_plan_), 4, "no back-propagation gather plan for this shape");
+    DAU_CHECK(plan_grad_tma(m.Nv, S, F_, G_, m.Hv, m.Wv, max_off_, num_sms_, &grad_plan_), 4, "no gradient plan for this shape");
     // forward workspace: blurred input | unit table | flag
     size_t o = 0;
-    const size_t blur_in = fwd_plan_.kind == 1 ? paired_layout_floats(m.Nv, S, m.Hv, m.Wv) : act_in;
-    const size_t blur_out = bwd_plan_.kind == 1 ? paired_layout_floats(m.Nv, F_, m.Hv, m.Wv) : act_out;
+    const size_t blur_in = paired_layout_floats(m.Nv, S, m.Hv, m.Wv);
+    const size_t blur_out = paired_layout_floats(m.Nv, F_, m.Hv, m.Wv);
     off_fwd_blur_ = o;  o = align_up(o + blur_in * sizeof(float));
     off_fwd_table_ = o; o = align_up(o + units * sizeof(UnitRec));
     off_fwd_flag_ = o;  o = align_up(o + 256);
     fwd_ws_ = o;
     // backward workspace: 4 derivative blurs | blurred error | two unit tables | split partials | flag
     o = 0;
-    const size_t xk_floats = grad_plan_.kind == 1 ? strip_layout_floats(m.Nv, S, m.Hv, m.Wv) : 4 * act_in;
-    const size_t esg_floats = grad_plan_.kind == 1 ? error_layout_floats(m.Nv, F_, m.Hv, m.Wv) : 0;
+    const size_t xk_floats = strip_layout_floats(m.Nv, S, m.Hv, m.Wv);
+    const size_t esg_floats = error_layout_floats(m.Nv, F_, m.Hv, m.Wv);
     off_bwd_xk_ = o;      o = align_up(o + xk_floats * sizeof(float));
     off_bwd_esg_ = o;     o = align_up(o + esg_floats * sizeof(float));
     off_bwd_eb_ = o;      o = align_up(o + blur_out * sizeof(float));
@@ -216,8 +213,7 @@ void DAUConvLayerB200::Forward_gpu(const float* bottom, float* w, float* mu1, fl
     const BlurFactors& f = factors_for(sigma, stream);
 
     tic(0, 1, stream);
-    if (fwd_plan_.kind == 1) launch_blur_single_paired(bottom, xb, mosaic_, S_, f.kb, f.fwd_x, f.fwd_y, stream);
-    else launch_blur_single(bottom, xb, N_ * S_, H_, W_, f.kb, f.fwd_x, f.fwd_y, stream);
+    launch_blur_single_paired(bottom, xb, mosaic_, S_, f.kb, f.fwd_x, f.fwd_y, stream);
     toc(0, 1, stream);
 
     tic(0, 2, stream);
@@ -231,10 +227,7 @@ void DAUConvLayerB200::Forward_gpu(const float* bottom, float* w, float* mu1, fl
     toc(0, 2, stream);
 
     tic(0, 3, stream);
-    if (fwd_plan_.kind == 1)
-        launch_gather_tma(fwd_plan_, xb, table, st_.bias_term ? bias : nullptr, top, mosaic_, S_, F_, G_, stream);
-    else
-        launch_gather(fwd_plan_, xb, table, st_.bias_term ? bias : nullptr, top, N_, S_, F_, G_, H_, W_, stream);
+    launch_gather_tma(fwd_plan_, xb, table, st_.bias_term ? bias : nullptr, top, mosaic_, S_, F_, G_, stream);
     toc(0, 3, stream);
 }
 
@@ -269,8 +262,7 @@ void DAUConvLayerB200::Backward_gpu(const float* bottom, const float* top_error,
 
     if (want_params) {
         tic(1, 0, stream);
-        if (grad_plan_.kind == 1) launch_blur_bank_strips(bottom, xk, mosaic_, S_, f, stream);
-        else launch_blur_bank(bottom, xk, N_ * S_, H_, W_, f, stream);
+        launch_blur_bank_strips(bottom, xk, mosaic_, S_, f, stream);
         toc(1, 0, stream);
     }
     {
@@ -285,12 +277,8 @@ void DAUConvLayerB200::Backward_gpu(const float* bottom, const float* top_error,
         tic(1, 2, stream);
         const int mrow = st_.ignore_edge_gradients && edge_rule(H_) ? 1 : 0;
         const int mcol = st_.ignore_edge_gradients && edge_rule(W_) ? 1 : 0;
-        if (grad_plan_.kind == 1) {
-            launch_error_relayout(top_error, esg, mosaic_, F_, mrow, mcol, stream);
-            launch_grad_tma(grad_plan_, xk, esg, gtable, partial, mosaic_.Nv, S_, F_, G_, mosaic_.Hv, mosaic_.Wv, stream);
-        } else {
-            launch_grad(grad_plan_, xk, top_error, gtable, partial, N_, S_, F_, G_, H_, W_, mrow, mcol, stream);
-        }
+        launch_error_relayout(top_error, esg, mosaic_, F_, mrow, mcol, stream);
+        launch_grad_tma(grad_plan_, xk, esg, gtable, partial, mosaic_.Nv, S_, F_, G_, mosaic_.Hv, mosaic_.Wv, stream);
         toc(1, 2, stream);
         tic(1, 3, stream);
         GradFinalizeArgs fa;
@@ -308,14 +296,10 @@ void DAUConvLayerB200::Backward_gpu(const float* bottom, const float* top_error,
         // blur the error with the rotated filter, then gather with -mu and the parameters read
         // transposed (base_dau_conv_layer.cu:278-325)
         tic(1, 4, stream);
-        if (bwd_plan_.kind == 1) launch_blur_single_paired(top_error, eb, mosaic_, F_, f.kb, f.err_x, f.err_y, stream);
-        else launch_blur_single(top_error, eb, N_ * F_, H_, W_, f.kb, f.err_x, f.err_y, stream);
+        launch_blur_single_paired(top_error, eb, mosaic_, F_, f.kb, f.err_x, f.err_y, stream);
         toc(1, 4, stream);
         tic(1, 5, stream);
-        if (bwd_plan_.kind == 1)
-            launch_gather_tma(bwd_plan_, eb, btable, nullptr, bottom_error, mosaic_, F_, S_, G_, stream);
-        else
-            launch_gather(bwd_plan_, eb, btable, nullptr, bottom_error, N_, F_, S_, G_, H_, W_, stream);
+        launch_gather_tma(bwd_plan_, eb, btable, nullptr, bottom_error, mosaic_, F_, S_, G_, stream);
         toc(1, 5, stream);
     }
     if ((flags & DAU_GRAD_BIAS) && st_.bias_term && dbias) {

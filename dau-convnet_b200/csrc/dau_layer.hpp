@@ -33,6 +33,9 @@ public:
                       float* dmu1, float* dmu2, float* dsigma, float* dbias, unsigned flags,
                       void* ws, size_t ws_bytes, cudaStream_t stream);
 
+    // sigma known to the caller: skips the blocking device read of sigma[0] in every call (the
+    // reference reads it once in LayerSetUp, base_dau_conv_layer.hpp:266-275).  Reshape sizes the
+    // mosaic gap from it, so set it BEFORE Reshape when sigma is larger than the op default 0.5.
     void set_sigma_hint(float v) { sigma_hint_ = v; }
     void enable_timing(bool e);
     int  get_timing(int which, float* ms, int cap);

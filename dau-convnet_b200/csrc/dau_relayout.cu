@@ -1,0 +1,48 @@
+// Re-layout of the top error for the gradient kernel (the blurs live in dau_blur_pair.cu).
+#include "dau_kernels.cuh"
+
+namespace dau {
+
+namespace {
+// top error NCHW -> SGP[n/2][f][y][x%2][x/2][n%2] of the MOSAIC image (row of x/2 padded to an even
+// count; gaps and cells beyond the batch are zeros), with the ignore_edge_gradients mask
+// (dau_conv_backward_core.hpp:2218-2222) applied on the way.  One thread moves the column pair
+// (2j, 2j+1) of both mosaic images of the pair; the float2 stores are coalesced.
+__global__ void __launch_bounds__(128) error_relayout_kernel(const float* __restrict__ err, float2* __restrict__ out,
+                                                             const __grid_constant__ Mosaic m, int F, int qp,
+                                                             int mask_row, int mask_col) {
+    const int pf = blockIdx.x;                            // (pair, feature)
+    const int np = pf / F, f = pf - np * F;
+    const int vy = blockIdx.y;
+    float2* dst = out + ((size_t)pf * m.Hv + vy) * 2 * qp;
+    const size_t rplane = (size_t)m.H * m.W;
+    for (int j = threadIdx.x; j < qp; j += 128) {
+        float v[2][2] = {{0.f, 0.f}, {0.f, 0.f}};         // [column 2j / 2j+1][image of the pair]
+#pragma unroll
+        for (int c = 0; c < 2; ++c)
+#pragma unroll
+            for (int img = 0; img < 2; ++img) {
+                const int vx = 2 * j + c, nv = 2 * np + img;
+                int rn, ry, rx;
+                if (vx < m.Wv && nv < m.Nv && mosaic_to_real(m, nv, vy, vx, &rn, &ry, &rx)) {
+                    const bool dead = (mask_row && ry == m.H - 1) || (mask_col && rx == m.W - 1);
+                    if (!dead) v[c][img] = __ldg(err + ((size_t)rn * F + f) * rplane + (size_t)ry * m.W + rx);
+                }
+            }
+        dst[j] = make_float2(v[0][0], v[0][1]);
+        dst[qp + j] = make_float2(v[1][0], v[1][1]);
+    }
+}
+}  // namespace
+
+void launch_error_relayout(const float* err, float* out_sg, const Mosaic& m, int F, int mask_row, int mask_col,
+                           cudaStream_t stream) {
+    const int qv = (m.Wv + 1) / 2, qp = (qv + 1) / 2 * 2;
+    const long long total = (long long)((m.Nv + 1) / 2) * F;
+    DAU_CHECK(total < (1LL << 31) && m.Hv <= 65535, 4, "shape too large for the error re-layout grid");
+    error_relayout_kernel<<<dim3((unsigned)total, m.Hv), 128, 0, stream>>>(err, reinterpret_cast<float2*>(out_sg), m, F, qp,
+                                                                           mask_row, mask_col);
+    DAU_CUDA_CHECK(cudaGetLastError());
+}
+
+}  // namespace dau

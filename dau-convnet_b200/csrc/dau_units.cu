@@ -46,7 +46,7 @@ __global__ void unit_prep_kernel(UnitPrepArgs a, UnitRec* __restrict__ fwd, Unit
         fwd[((size_t)s * a.F + f) * a.G + g] = r;
     }
     if (grad) {
-        // gather of the ERROR around p' - o - 1 (see dau_grad.cu); tap order flips
+        // gather of the ERROR around p' - o - 1 (see dau_grad_tma.cu); tap order flips
         UnitRec r;
         r.w00 = b11; r.w01 = b10; r.w10 = b01; r.w11 = b00;
         r.offx_h = -ox - 1 + a.ghalo_x; r.offy_h = -oy - 1 + a.ghalo_y; r.pad0 = 0; r.pad1 = 0;

@@ -63,6 +63,7 @@ class DAULayerHandle(object):
         idx = self.device.index if self.device.index is not None else torch.cuda.current_device()
         _lib.check(_lib.lib.dau_create(C.byref(settings), idx, C.byref(self._h)))
         self._shape = None
+        self._hint = None
         self._ws = None
         self.fwd_bytes = self.bwd_bytes = 0
 
@@ -75,11 +76,12 @@ class DAULayerHandle(object):
             pass
 
     def reshape(self, N, S, H, W):
-        if self._shape != (N, S, H, W):
+        # the layer plans its layouts (mosaic gap) from the shape AND the blur width, i.e. sigma
+        if self._shape != (N, S, H, W, self._hint):
             f, b = C.c_size_t(0), C.c_size_t(0)
             _lib.check(_lib.lib.dau_reshape(self._h, N, S, H, W, C.byref(f), C.byref(b)))
             self.fwd_bytes, self.bwd_bytes = f.value, b.value
-            self._shape = (N, S, H, W)
+            self._shape = (N, S, H, W, self._hint)
 
     def workspace(self, nbytes):
         if self._ws is None or self._ws.numel() < nbytes:
@@ -87,7 +89,12 @@ class DAULayerHandle(object):
         return self._ws
 
     def set_sigma_hint(self, value):
-        _lib.check(_lib.lib.dau_set_sigma_hint(self._h, float(value)))
+        """Tell the layer sigma's value (it is one number per layer, base_dau_conv_layer.hpp:150):
+        without it every call reads sigma[0] back from the device with a blocking copy."""
+        value = float(value)
+        if value != self._hint:
+            _lib.check(_lib.lib.dau_set_sigma_hint(self._h, value))
+            self._hint = value
 
     def enable_timing(self, enable=True):
         _lib.check(_lib.lib.dau_enable_timing(self._h, int(enable)))
@@ -166,6 +173,7 @@ def dau_conv_op(input, weights, mu1, mu2, sigma, **attrs):
     """TF op DAUConv: output[N,F,H,W] (forward only, no autograd)."""
     _check_inputs(input, weights, mu1, mu2, sigma, attrs)
     h = get_handle(input.device, **attrs)
+    h.set_sigma_hint(float(sigma.reshape(-1)[0]))        # the TF op builds its layer from the live sigma
     return h.forward(input.contiguous(), weights.contiguous(), mu1.contiguous(), mu2.contiguous(),
                      sigma.contiguous())
 
@@ -174,6 +182,7 @@ def dau_conv_grad_op(grad, input, weights, mu1, mu2, sigma, **attrs):
     """TF op DAUConvGrad: (grad_input, grad_weights, grad_mu1, grad_mu2, grad_sigma)."""
     _check_inputs(input, weights, mu1, mu2, sigma, attrs)
     h = get_handle(input.device, **attrs)
+    h.set_sigma_hint(float(sigma.reshape(-1)[0]))
     return h.backward(input.contiguous(), grad.contiguous(), weights.contiguous(), mu1.contiguous(),
                       mu2.contiguous(), sigma.contiguous())
 
@@ -198,6 +207,7 @@ class _DAUConvFunction(torch.autograd.Function):
             flags |= _lib.GRAD_W | _lib.GRAD_MU1 | _lib.GRAD_MU2 | _lib.GRAD_SIGMA
         _check_inputs(input, weights, mu1, mu2, sigma, ctx.attrs)
         h = get_handle(input.device, **ctx.attrs)
+        h.set_sigma_hint(float(sigma.reshape(-1)[0]))
         dx, dw, dm1, dm2, dsg = h.backward(input.contiguous(), grad.contiguous(), weights.contiguous(),
                                            mu1.contiguous(), mu2.contiguous(), sigma.contiguous(), flags=flags)
         return (dx if need[0] else None, dw if need[1] else None, dm1 if need[2] else None,

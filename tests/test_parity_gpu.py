@@ -77,6 +77,9 @@ SHAPES = [
     (2, 30, 21, 5, 7, (1, 3), 9, 3.9), (2, 6, 6, 16, 24, (2, 1), 17, 8),
     (1, 40, 40, 2, 3, (1, 1), 65, 20), (2, 17, 70, 4, 9, (3, 3), 9, 2),
     (2, 20, 20, 2, 2, (3, 6), 9, 3),
+    # narrow maps packed into mosaics (several images per 64-px tile, cells beyond the batch)
+    (16, 13, 13, 8, 8, (1, 2), 9, 3.9), (9, 13, 13, 3, 5, (1, 2), 9, 3.9), (12, 27, 27, 4, 6, (1, 2), 9, 3.9),
+    (8, 28, 28, 4, 4, (1, 2), 17, 8), (33, 6, 5, 2, 3, (2, 2), 9, 3.9),
 ]
 
 
@@ -100,6 +103,17 @@ def test_oracle_parity(shape, edge):
     y, g = run_layer(x, err, w, mu1, mu2, 0.5, ks, unit_testing=edge)
     close(y, O.forward(x, w, mu1, mu2, [0.5]), "y")
     ref = O.backward(x, err, w, mu1, mu2, [0.5], ignore_edge_gradients=edge)
+    for got, r, name in zip(g, ref, ("dx", "dw", "dmu1", "dmu2", "dsigma")):
+        close(got, r, name, scale_atol=name != "dx")
+
+
+@pytest.mark.parametrize("sigma", [0.8, 1.2, 1.6])
+def test_wide_blur_in_mosaic(sigma):
+    """Blur half-width (4, 6, 8) >= the displacement bound: the mosaic gap must follow sigma."""
+    x, err, w, mu1, mu2, ks = _case((10, 13, 11, 3, 4, (1, 2), 9, 3.9), 77)
+    y, g = run_layer(x, err, w, mu1, mu2, sigma, ks, unit_testing=False)
+    close(y, O.forward(x, w, mu1, mu2, [sigma]), "y")
+    ref = O.backward(x, err, w, mu1, mu2, [sigma], ignore_edge_gradients=False)
     for got, r, name in zip(g, ref, ("dx", "dw", "dmu1", "dmu2", "dsigma")):
         close(got, r, name, scale_atol=name != "dx")
 

@@ -27,6 +27,7 @@ mu1 = (torch.rand((1, S, G, F), device=dev) * 2 * m - m).clamp(-m + 0.01, m - 0.
 mu2 = (torch.rand((1, S, G, F), device=dev) * 2 * m - m).clamp(-m + 0.01, m - 0.01)
 sg = torch.full((1, S, G, F), 0.5, device=dev)
 h = dau_conv.get_handle(dev, num_output=F, number_units_x=1, number_units_y=G, kernel_size=a.ks, pad=m)
+h.set_sigma_hint(0.5)
 h.enable_timing(True)
 U = N * F * S * G * H * W
 for it in range(a.iters):
