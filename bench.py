@@ -254,18 +254,14 @@ def run_ours(args, rank, world, local_rank):
     yp = torch.empty((N, F, H, W), dtype=torch.float32).pin_memory()
     dxp = torch.empty((N, S, H, W), dtype=torch.float32).pin_memory()
     gp = torch.empty((4, 1, S, G, F), dtype=torch.float32).pin_memory()
-    xd, ed = torch.empty_like(x), torch.empty_like(e)
 
     def e2e_step():
-        xd.copy_(xp, non_blocking=True)
-        ed.copy_(ep, non_blocking=True)
-        h.forward(xd, w, mu1, mu2, sigma, out=y)
+        # the public host-buffer call: chunked H2D -> fwd+bwd -> D2H, copies overlapped with kernels
         flat.zero_()
-        out = h.backward(xd, ed, w, mu1, mu2, sigma, grads=grads)
+        h.train_step_host(xp, ep, w, mu1, mu2, sigma, 0.5, y_host=yp, dx_host=dxp, grads=grads,
+                          chunk_images=args.e2e_chunk)
         if world > 1:
             dist.all_reduce(flat)
-        yp.copy_(y, non_blocking=True)
-        dxp.copy_(out[0], non_blocking=True)
         gp.copy_(flat, non_blocking=True)
 
     e2e_step()
@@ -299,8 +295,9 @@ def run_ours(args, rank, world, local_rank):
                    "l2": "inputs larger than L2 (x and top_error are %.0f MB each; L2 is 126 MB)" % (xh.nbytes / 1e6)},
         "roofline": roofline, "cpu_baseline": cpu_baseline,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "steps": e2e_steps, "what": "pinned host x, top_error -> device; fwd+bwd; y, dL/dx and the "
-                                             "4 parameter gradients -> pinned host"},
+                "steps": e2e_steps, "chunk_images": args.e2e_chunk,
+                "what": "dau_train_step_host: pinned host x, top_error -> device; fwd+bwd; y, dL/dx and the "
+                        "4 parameter gradients -> pinned host; copies overlapped with the kernels chunk by chunk"},
         "gpu_launches": launches, "clocks": sampler.summary() if sampler else None,
     }))
 
@@ -314,6 +311,7 @@ def main():
     ap.add_argument("--config", default="c2", choices=sorted(CONFIGS))
     ap.add_argument("--cpu-sample", type=int, default=4, help="images per CPU-baseline pass")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--e2e-chunk", type=int, default=16, help="images per chunk of the host-buffer step")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

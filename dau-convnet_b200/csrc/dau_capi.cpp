@@ -1,6 +1,7 @@
 // extern "C" boundary of libdau_conv_b200.so (include/dau_conv_b200.h).  Exceptions of the
 // C++ layer (DAUException, the reference's error convention) become status codes plus a
 // thread-local message.
+#include "dau_host_step.hpp"
 #include "dau_layer.hpp"
 
 #include <cstdio>
@@ -9,7 +10,7 @@
 
 using dau::DAUConvLayerB200;
 
-struct dau_handle_s { DAUConvLayerB200* layer; };
+struct dau_handle_s { DAUConvLayerB200* layer; dau::HostPipeline* pipe; };
 
 namespace {
 thread_local char g_err[1024] = "";
@@ -83,12 +84,14 @@ dau_status_t dau_create(const dau_settings_t* settings, int device, dau_handle_t
         DAUConvLayerB200* l = new DAUConvLayerB200(*settings, device);
         dau_handle_t* h = new dau_handle_t;
         h->layer = l;
+        h->pipe = nullptr;
         *out = h;
     });
 }
 
 void dau_destroy(dau_handle_t* h) {
     if (!h) return;
+    delete h->pipe;
     delete h->layer;
     delete h;
 }
@@ -186,6 +189,20 @@ dau_status_t dau_backward_host(dau_handle_t* h, int N, int S, int H, int W, cons
     });
 }
 
+dau_status_t dau_train_step_host(dau_handle_t* h, int N, int S, int H, int W, int chunk_images,
+                                 float sigma_value, const float* x_host, const float* top_error_host,
+                                 float* w, float* mu1, float* mu2, float* sigma, float* y_host,
+                                 float* dx_host, float* dw, float* dmu1, float* dmu2, float* dsigma,
+                                 void* stream) {
+    if (!h) return fail(DAU_ERR_INVALID_ARGUMENT, "dau_train_step_host: NULL handle");
+    return guarded([&] {
+        DAU_CHECK(!h->layer->settings().bias_term, 4, "dau_train_step_host: bias_term is not supported");
+        if (!h->pipe) h->pipe = new dau::HostPipeline(h->layer->settings(), h->layer->device());
+        h->pipe->step(N, S, H, W, chunk_images, sigma_value, x_host, top_error_host, w, mu1, mu2, sigma,
+                      y_host, dx_host, dw, dmu1, dmu2, dsigma, (cudaStream_t)stream);
+    });
+}
+
 dau_status_t dau_measure_fma_peak(int device, int iters, double* tflops_out, double* ms_out) {
     return guarded([&] {
         DAU_CUDA_CHECK(cudaSetDevice(device));
@@ -223,6 +240,8 @@ dau_status_t dau_get_timing(dau_handle_t* h, int which, float* ms_out, int capac
 
 const char* dau_timing_name(int which, int index) { return DAUConvLayerB200::timing_name(which, index); }
 
-long long dau_launch_count(const dau_handle_t* h) { return h ? h->layer->launches() : 0; }
+long long dau_launch_count(const dau_handle_t* h) {
+    return h ? h->layer->launches() + (h->pipe ? h->pipe->launches() : 0) : 0;
+}
 
 }  // extern "C"

@@ -140,6 +140,25 @@ class DAULayerHandle(object):
         return (dx,) + tuple(grads)
 
 
+    def train_step_host(self, x_host, err_host, w, mu1, mu2, sigma, sigma_value, y_host=None, dx_host=None,
+                        grads=None, chunk_images=16):
+        """dau_train_step_host: forward + backward on HOST tensors (pin them), copies overlapped
+        with the kernels chunk by chunk; parameter gradients accumulate into `grads` (device)."""
+        N, S, H, W = x_host.shape
+        for t in (x_host, err_host, y_host, dx_host):
+            if t is not None and (t.is_cuda or t.dtype != torch.float32 or not t.is_contiguous()):
+                raise RuntimeError("train_step_host: activations must be contiguous float32 host tensors")
+        if grads is None:
+            grads = [torch.zeros_like(w) for _ in range(4)]
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        _lib.check(_lib.lib.dau_train_step_host(
+            self._h, N, S, H, W, int(chunk_images), float(sigma_value), x_host.data_ptr(), err_host.data_ptr(),
+            w.data_ptr(), mu1.data_ptr(), mu2.data_ptr(), sigma.data_ptr(),
+            y_host.data_ptr() if y_host is not None else None, dx_host.data_ptr() if dx_host is not None else None,
+            grads[0].data_ptr(), grads[1].data_ptr(), grads[2].data_ptr(), grads[3].data_ptr(), stream))
+        return grads
+
+
 _HANDLES = {}
 
 

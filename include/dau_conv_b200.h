@@ -128,6 +128,21 @@ dau_status_t dau_backward_host(dau_handle_t* h, int N, int S, int H, int W, cons
                                float* dw, float* dmu1, float* dmu2, float* dsigma, float* dbias,
                                unsigned flags);
 
+/* One training step (dau_forward + dau_backward, all gradients) on a batch that lives in HOST
+ * memory, cut into chunks of `chunk_images` whose PCIe copies overlap the kernels of the
+ * neighbouring chunks (three internal streams, double-buffered staging owned by the handle).
+ * x, top_error, y, dx: host pointers, NCHW fp32 (pinned memory for real overlap; y / dx may be
+ * NULL).  Parameters and parameter gradients: DEVICE pointers [1,S,G,F]; the gradients are
+ * accumulated into, as in dau_backward.  Stream-ordered with respect to `stream`, asynchronous
+ * to the host.  sigma_value: the layer's sigma (it is one number, base_dau_conv_layer.hpp:150).
+ * Replaces, for a host outside a CUDA framework, the sequence  H2D -> DAUConv -> DAUConvGrad ->
+ * D2H  around plugins/tensorflow/src/dau_conv_op.cpp:150-324 / dau_conv_grad_op.cpp:115-318. */
+dau_status_t dau_train_step_host(dau_handle_t* h, int N, int S, int H, int W, int chunk_images,
+                                 float sigma_value, const float* x_host, const float* top_error_host,
+                                 float* w_dev, float* mu1_dev, float* mu2_dev, float* sigma_dev,
+                                 float* y_host, float* dx_host, float* dw_dev, float* dmu1_dev,
+                                 float* dmu2_dev, float* dsigma_dev, void* stream);
+
 /* Measurement helpers used by bench.py (not part of the reference contract). */
 dau_status_t dau_measure_fma_peak(int device, int iters, double* tflops_out, double* ms_out);
 /* Per-kernel device times (ms) of the last forward / backward on this handle, measured with

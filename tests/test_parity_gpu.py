@@ -158,6 +158,28 @@ def test_mu_learning_rate_factor_and_accumulation():
     np.testing.assert_allclose(grads[0].cpu().numpy(), g1[1] + 2.0, rtol=1e-6, atol=1e-6)
 
 
+def test_host_training_step_matches_device_path():
+    """dau_train_step_host (chunked, copy/compute overlapped) == dau_forward + dau_backward."""
+    import torch
+    import dau_conv
+    x, err, w, mu1, mu2, ks = _case((11, 20, 14, 5, 6, (1, 2), 9, 3.9), 5)
+    y_ref, g_ref = run_layer(x, err, w, mu1, mu2, 0.5, ks)
+    dev = torch.device("cuda:0")
+    sig = np.full(w.shape, 0.5, np.float32)
+    wd, m1, m2, sg = [torch.from_numpy(a).to(dev) for a in (w, mu1, mu2, sig)]
+    h = dau_conv.get_handle(dev, num_output=6, number_units_x=1, number_units_y=2, kernel_size=ks, pad=4)
+    xp, ep = torch.from_numpy(x).pin_memory(), torch.from_numpy(err).pin_memory()
+    for chunk in (4, 11, 64):                       # ragged tail, one chunk, chunk > batch
+        yp = torch.zeros(y_ref.shape).pin_memory()
+        dxp = torch.zeros(x.shape).pin_memory()
+        grads = h.train_step_host(xp, ep, wd, m1, m2, sg, 0.5, y_host=yp, dx_host=dxp, chunk_images=chunk)
+        torch.cuda.synchronize()
+        assert np.array_equal(yp.numpy(), y_ref), chunk          # per-image work: bit-identical
+        assert np.array_equal(dxp.numpy(), g_ref[0]), chunk
+        for got, r, name in zip(grads, g_ref[1:], ("dw", "dmu1", "dmu2", "dsigma")):
+            close(got.cpu().numpy(), r, name, scale_atol=True)   # chunking reorders the fp32 sums
+
+
 def test_full_size_properties_config_c2():
     """BASELINE config C2 (N=128, S=F=128, 64x64, G=4): size-independent identities.
     (a) sum(E*Y) == sum_units w*dL/dw  (Y is linear in w; a checksum of all 3.4e10 unit-pixels)
