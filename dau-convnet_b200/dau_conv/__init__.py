@@ -3,6 +3,8 @@
 from . import _lib
 from ._lib import DAUError, default_settings, get_kernels
 from .functional import (DAULayerHandle, dau_conv, dau_conv_grad_op, dau_conv_op, get_handle)
+from .layers import DAUConv1d, DAUConv2d, dau_conv2d, dau_grid_mean, zero_n_last
 
 __all__ = ["DAUError", "default_settings", "get_kernels", "DAULayerHandle", "dau_conv",
-           "dau_conv_op", "dau_conv_grad_op", "get_handle"]
+           "dau_conv_op", "dau_conv_grad_op", "get_handle", "DAUConv2d", "DAUConv1d", "dau_conv2d",
+           "dau_grid_mean", "zero_n_last"]

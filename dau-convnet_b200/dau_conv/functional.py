@@ -188,20 +188,26 @@ def _check_inputs(x, w, mu1, mu2, sigma, attrs):
             raise RuntimeError("DAUConv: %s has shape %s, expected %s" % (name, tuple(t.shape), want))
 
 
-def dau_conv_op(input, weights, mu1, mu2, sigma, **attrs):
+def _sigma_of(sigma, sigma_value):
+    # the TF op builds its layer from the live sigma (one number per layer); a caller that knows
+    # the value passes it and spares the blocking device read
+    return float(sigma.reshape(-1)[0]) if sigma_value is None else float(sigma_value)
+
+
+def dau_conv_op(input, weights, mu1, mu2, sigma, sigma_value=None, **attrs):
     """TF op DAUConv: output[N,F,H,W] (forward only, no autograd)."""
     _check_inputs(input, weights, mu1, mu2, sigma, attrs)
     h = get_handle(input.device, **attrs)
-    h.set_sigma_hint(float(sigma.reshape(-1)[0]))        # the TF op builds its layer from the live sigma
+    h.set_sigma_hint(_sigma_of(sigma, sigma_value))
     return h.forward(input.contiguous(), weights.contiguous(), mu1.contiguous(), mu2.contiguous(),
                      sigma.contiguous())
 
 
-def dau_conv_grad_op(grad, input, weights, mu1, mu2, sigma, **attrs):
+def dau_conv_grad_op(grad, input, weights, mu1, mu2, sigma, sigma_value=None, **attrs):
     """TF op DAUConvGrad: (grad_input, grad_weights, grad_mu1, grad_mu2, grad_sigma)."""
     _check_inputs(input, weights, mu1, mu2, sigma, attrs)
     h = get_handle(input.device, **attrs)
-    h.set_sigma_hint(float(sigma.reshape(-1)[0]))
+    h.set_sigma_hint(_sigma_of(sigma, sigma_value))
     return h.backward(input.contiguous(), grad.contiguous(), weights.contiguous(), mu1.contiguous(),
                       mu2.contiguous(), sigma.contiguous())
 
@@ -210,10 +216,11 @@ class _DAUConvFunction(torch.autograd.Function):
     """@ops.RegisterGradient("DAUConv") equivalent (_dau_conv_grad_op.py:14-60)."""
 
     @staticmethod
-    def forward(ctx, input, weights, mu1, mu2, sigma, attrs):
+    def forward(ctx, input, weights, mu1, mu2, sigma, attrs, sigma_value):
         ctx.attrs = attrs
+        ctx.sigma_value = _sigma_of(sigma, sigma_value)
         ctx.save_for_backward(input, weights, mu1, mu2, sigma)
-        return dau_conv_op(input, weights, mu1, mu2, sigma, **attrs)
+        return dau_conv_op(input, weights, mu1, mu2, sigma, sigma_value=ctx.sigma_value, **attrs)
 
     @staticmethod
     def backward(ctx, grad):
@@ -226,13 +233,13 @@ class _DAUConvFunction(torch.autograd.Function):
             flags |= _lib.GRAD_W | _lib.GRAD_MU1 | _lib.GRAD_MU2 | _lib.GRAD_SIGMA
         _check_inputs(input, weights, mu1, mu2, sigma, ctx.attrs)
         h = get_handle(input.device, **ctx.attrs)
-        h.set_sigma_hint(float(sigma.reshape(-1)[0]))
+        h.set_sigma_hint(ctx.sigma_value)
         dx, dw, dm1, dm2, dsg = h.backward(input.contiguous(), grad.contiguous(), weights.contiguous(),
                                            mu1.contiguous(), mu2.contiguous(), sigma.contiguous(), flags=flags)
         return (dx if need[0] else None, dw if need[1] else None, dm1 if need[2] else None,
-                dm2 if need[3] else None, dsg if need[4] else None, None)
+                dm2 if need[3] else None, dsg if need[4] else None, None, None)
 
 
-def dau_conv(input, weights, mu1, mu2, sigma, **attrs):
+def dau_conv(input, weights, mu1, mu2, sigma, sigma_value=None, **attrs):
     """Differentiable DAUConv (forward + registered gradient)."""
-    return _DAUConvFunction.apply(input, weights, mu1, mu2, sigma, attrs)
+    return _DAUConvFunction.apply(input, weights, mu1, mu2, sigma, attrs, sigma_value)
