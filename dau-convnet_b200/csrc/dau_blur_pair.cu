@@ -22,6 +22,20 @@
 namespace dau {
 
 namespace {
+__device__ __forceinline__ void cp_async4_zfill(float* dst, const float* src, bool ok) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(dst);
+    const int sz = ok ? 4 : 0;
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;\n" ::"r"(d), "l"(src), "r"(sz) : "memory");
+}
+__device__ __forceinline__ void cp_async16_zfill(float* dst, const float* src, bool ok) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(dst);
+    const int sz = ok ? 16 : 0;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(d), "l"(src), "r"(sz) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
+
 constexpr int PT_W = 64, PT_H = 32, PT_THREADS = 256;
 constexpr int PT_MAXTAPS = 17;
 
@@ -42,37 +56,60 @@ blur_pair_kernel(const float* __restrict__ in, float* __restrict__ out, const __
     constexpr int PADX = 4 * CQ, NT = 8 * CQ + 1, SW = PT_W + 2 * PADX, NV = 2 * CQ + 1;
     extern __shared__ float4 smem4[];
     const int c = a.kb >> 1, rows = PT_H + 2 * c;
-    float* s_in = reinterpret_cast<float*>(smem4);          // [rows][SW]
-    float* s_h = s_in + rows * SW;                           // [NH][rows][PT_W]
+    float* s_in0 = reinterpret_cast<float*>(smem4);         // [2 images][rows][SW]
+    float* s_h = s_in0 + 2 * rows * SW;                      // [NH][rows][PT_W]
     const int tid = threadIdx.x;
     const int x0 = blockIdx.x * PT_W, y0 = blockIdx.y * PT_H;
     const int pc = a.z0 + blockIdx.z;                        // (pair, channel)
     const int np = pc / a.Cn, cn = pc - np * a.Cn;
     const int H = a.H, W = a.W;
+    constexpr bool ident = IDENT;
+    const size_t rplane = (size_t)a.m.H * a.m.W;
 
-    float4 res[2][2][NOUT];
+    // ---- stage the haloed tiles of BOTH images with cp.async (zero fill outside the image): the
+    //      second image's HBM latency hides behind the first image's filtering --------------------
+    const bool vec16 = ident && (W & 3) == 0 && (reinterpret_cast<size_t>(in) & 15) == 0;
 #pragma unroll
     for (int img = 0; img < 2; ++img) {
         const int n = 2 * np + img;                          // mosaic image
         const bool live = n < a.N;
-        constexpr bool ident = IDENT;
-        const size_t rplane = (size_t)a.m.H * a.m.W;
-        // ---- stage the haloed tile, zero outside the image --------------------------------------
-        for (int i = tid; i < rows * SW; i += PT_THREADS) {
-            const int r = i / SW, q = i - r * SW;
-            const int gy = y0 + r - c, gx = x0 + q - PADX;
-            float v = 0.f;
-            if (live && gy >= 0 && gy < H && gx >= 0 && gx < W) {
-                if (ident) {
-                    v = __ldg(in + ((size_t)n * a.Cn + cn) * rplane + (size_t)gy * W + gx);
-                } else {
-                    int rn, ry, rx;
-                    if (mosaic_to_real(a.m, n, gy, gx, &rn, &ry, &rx))
-                        v = __ldg(in + ((size_t)rn * a.Cn + cn) * rplane + (size_t)ry * a.m.W + rx);
-                }
+        float* dst = s_in0 + img * rows * SW;
+        if (vec16) {
+            const float* src = in + ((size_t)n * a.Cn + cn) * rplane;
+            for (int i = tid; i < rows * (SW / 4); i += PT_THREADS) {
+                const int r = i / (SW / 4), q = (i - r * (SW / 4)) * 4;
+                const int gy = y0 + r - c, gx = x0 + q - PADX;       // gx % 4 == 0: all in or all out
+                const bool ok = live && gy >= 0 && gy < H && gx >= 0 && gx < W;
+                cp_async16_zfill(dst + r * SW + q, ok ? src + (size_t)gy * W + gx : in, ok);
             }
-            s_in[i] = v;
+        } else {
+            for (int i = tid; i < rows * SW; i += PT_THREADS) {
+                const int r = i / SW, q = i - r * SW;
+                const int gy = y0 + r - c, gx = x0 + q - PADX;
+                const float* src = in;
+                bool ok = live && gy >= 0 && gy < H && gx >= 0 && gx < W;
+                if (ok) {
+                    if (ident) {
+                        src = in + ((size_t)n * a.Cn + cn) * rplane + (size_t)gy * W + gx;
+                    } else {
+                        int rn, ry, rx;
+                        ok = mosaic_to_real(a.m, n, gy, gx, &rn, &ry, &rx);
+                        if (ok) src = in + ((size_t)rn * a.Cn + cn) * rplane + (size_t)ry * a.m.W + rx;
+                    }
+                }
+                cp_async4_zfill(dst + i, src, ok);
+            }
         }
+        cp_async_commit();
+    }
+
+    float4 res[2][2][NOUT];
+#pragma unroll
+    for (int img = 0; img < 2; ++img) {
+        const int n = 2 * np + img;
+        const bool live = n < a.N;
+        const float* s_in = s_in0 + img * rows * SW;
+        if (img == 0) cp_async_wait<1>(); else cp_async_wait<0>();
         __syncthreads();
         // ---- row pass: 4 outputs per task --------------------------------------------------------
         for (int t = tid; t < rows * (PT_W / 4); t += PT_THREADS) {
@@ -195,7 +232,7 @@ template <int MODE>
 void launch_pair(const float* in, float* out, PairBlurArgs& a, int pairs_times_c, cudaStream_t stream) {
     const int c = a.kb >> 1, cq = cq_of(a.kb);
     const int rows = PT_H + 2 * c, sw = PT_W + 8 * cq, nh = MODE == 3 ? 3 : 1;
-    const size_t smem = (size_t)(rows * sw + nh * rows * PT_W) * sizeof(float);
+    const size_t smem = (size_t)(2 * rows * sw + nh * rows * PT_W) * sizeof(float);
     static bool attr_set = false;
     if (!attr_set) {
         DAU_CUDA_CHECK(cudaFuncSetAttribute(blur_pair_kernel<MODE, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));

@@ -355,7 +355,7 @@ void launch_grad_tma(const GradPlan& plan, const float* xk_strips, const float* 
     p.items_per_split = (p.items + plan.n_splits - 1) / plan.n_splits;
     p.feat_bytes_al = plan.feat_stride * 4;
     p.stage_bytes = plan.feats_per_cta * plan.feat_stride * 4;
-    p.debug = getenv("DAU_DEBUG") ? atoi(getenv("DAU_DEBUG")) : 0;
+    p.debug = getenv("DAU_DEBUG_GRAD") ? atoi(getenv("DAU_DEBUG_GRAD")) : 0;
     switch (plan.variant) {
         case 0: launch_t<4>(plan, map, p, stream); break;
         case 1: launch_t<8>(plan, map, p, stream); break;
