@@ -43,7 +43,10 @@ namespace {
 
 using namespace tma;
 
-constexpr int R = 8, C = 4, LX = 16, LY = 2, NW = 8;
+constexpr int R = 16, C = 4, LX = 16, LY = 2, NW = 8;
+// CTA = 3 warpgroups: warpgroup 0 holds the producer lane and gives its registers away
+// (setmaxnreg.dec), warpgroups 1-2 are the 8 consumer warps and grow to CONS_REGS each.
+constexpr int NTHREADS = (NW + 4) * 32, PROD_REGS = 40, CONS_REGS = 232;
 constexpr int TW = LX * C, TH = LY * R;
 
 template <int HALO>
@@ -66,7 +69,7 @@ struct TGatherParams {
 };
 
 template <int HALO>
-__global__ void __launch_bounds__((NW + 1) * 32, 1)
+__global__ void __launch_bounds__(NTHREADS, 1)
 dau_gather_tma_kernel(const __grid_constant__ CUtensorMap in_map, const TGatherParams p) {
     using GEO = TGeom<HALO>;
     constexpr int QS = GEO::QS, ROW = GEO::ROW;
@@ -75,7 +78,8 @@ dau_gather_tma_kernel(const __grid_constant__ CUtensorMap in_map, const TGatherP
     // TMA destinations must be 128-byte aligned; the dynamic segment carries 128 spare bytes
     unsigned char* smem_raw = smem_dyn + ((128u - (smem_u32(smem_dyn) & 127u)) & 127u);
 
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int warp = (tid >> 5) - 4;               // consumer warp 0..7; negative: producer warpgroup
     const int tyi = blockIdx.x / p.tiles_x, txi = blockIdx.x - tyi * p.tiles_x;
     const int x0 = txi * TW, y0 = tyi * TH;
     const int np = blockIdx.z;                 // image pair
@@ -89,9 +93,10 @@ dau_gather_tma_kernel(const __grid_constant__ CUtensorMap in_map, const TGatherP
     }
     __syncthreads();
 
-    if (warp == NW) {
-        // ---- producer warp: one lane streams the input channels --------------------------------
-        if (lane == 0) {
+    if (warp < 0) {
+        // ---- producer warpgroup: one lane streams the input channels ----------------------------
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;\n" ::"n"(PROD_REGS));
+        if (warp == -4 && lane == 0) {
             if (!(p.debug & 1)) prefetch_map(&in_map);
             const uint32_t tx_bytes = ((p.debug & 2) ? 0 : GEO::TILE_BYTES) + ((p.debug & 4) ? 0 : nrec * (uint32_t)sizeof(UnitRec));
             for (int ci = 0; ci < p.Cin; ++ci) {
@@ -108,6 +113,7 @@ dau_gather_tma_kernel(const __grid_constant__ CUtensorMap in_map, const TGatherP
     }
 
     // ---- consumer warps ---------------------------------------------------------------------------
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;\n" ::"n"(CONS_REGS));
     const int lx = lane & (LX - 1), ly = lane >> 4;
     const int co = co0 + warp;
     const bool co_valid = co < p.Cout;
@@ -216,7 +222,7 @@ void launch_t(const GatherPlan& plan, const CUtensorMap& map, const TGatherParam
         attr_set = true;
     }
     dim3 grid(plan.grid_x, plan.grid_y, plan.grid_z);
-    dau_gather_tma_kernel<HALO><<<grid, (NW + 1) * 32, plan.smem_bytes, stream>>>(map, p);
+    dau_gather_tma_kernel<HALO><<<grid, NTHREADS, plan.smem_bytes, stream>>>(map, p);
 }
 
 template <int HALO>
