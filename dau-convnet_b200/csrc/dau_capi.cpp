@@ -203,6 +203,25 @@ dau_status_t dau_train_step_host(dau_handle_t* h, int N, int S, int H, int W, in
     });
 }
 
+dau_status_t dau_plan_mosaic(int N, int H, int W, int gap, int* out10) {
+    if (!out10) return fail(DAU_ERR_INVALID_ARGUMENT, "dau_plan_mosaic: NULL output");
+    return guarded([&] {
+        DAU_CHECK(N > 0 && H > 0 && W > 0 && gap >= 0, 1, "dau_plan_mosaic: sizes must be positive");
+        const dau::Mosaic m = dau::plan_mosaic(N, H, W, gap);
+        const int v[10] = {m.kx, m.ky, m.px, m.py, m.W, m.H, m.Wv, m.Hv, m.Nv, m.gap};
+        std::memcpy(out10, v, sizeof(v));
+    });
+}
+
+int dau_mosaic_to_real(const int* q, int N, int nv, int vy, int vx, int* n, int* y, int* x) {
+    if (!q || !n || !y || !x) return 0;
+    dau::Mosaic m;
+    m.kx = q[0]; m.ky = q[1]; m.px = q[2]; m.py = q[3]; m.W = q[4]; m.H = q[5]; m.Wv = q[6]; m.Hv = q[7];
+    m.Nv = q[8]; m.gap = q[9]; m.N = N;
+    if (nv < 0 || vy < 0 || vx < 0 || vy >= m.Hv || vx >= m.Wv || nv >= m.Nv) return 0;
+    return dau::mosaic_to_real(m, nv, vy, vx, n, y, x) ? 1 : 0;
+}
+
 dau_status_t dau_measure_fma_peak(int device, int iters, double* tflops_out, double* ms_out) {
     return guarded([&] {
         DAU_CUDA_CHECK(cudaSetDevice(device));

@@ -13,7 +13,7 @@ LIB_PATH = os.path.join(_HERE, "libdau_conv_b200.so")
 SYMBOLS = [
     "dau_last_error", "dau_abi_version", "dau_settings_default", "dau_create", "dau_destroy",
     "dau_reshape", "dau_set_sigma_hint", "dau_forward", "dau_backward", "dau_get_kernels",
-    "dau_forward_host", "dau_backward_host", "dau_train_step_host", "dau_measure_fma_peak", "dau_enable_timing",
+    "dau_forward_host", "dau_backward_host", "dau_train_step_host", "dau_plan_mosaic", "dau_mosaic_to_real", "dau_measure_fma_peak", "dau_enable_timing",
     "dau_get_timing", "dau_timing_name", "dau_launch_count",
 ]
 
@@ -61,6 +61,9 @@ lib.dau_get_kernels.argtypes = [C.POINTER(Settings), C.c_float, C.POINTER(C.c_in
 lib.dau_forward_host.argtypes = [_vp, C.c_int, C.c_int, C.c_int, C.c_int] + [_vp] * 7
 lib.dau_backward_host.argtypes = [_vp, C.c_int, C.c_int, C.c_int, C.c_int] + [_vp] * 13 + [C.c_uint]
 lib.dau_train_step_host.argtypes = [_vp] + [C.c_int] * 5 + [C.c_float] + [_vp] * 12 + [_vp]
+lib.dau_plan_mosaic.argtypes = [C.c_int] * 4 + [C.POINTER(C.c_int)]
+lib.dau_mosaic_to_real.argtypes = [C.POINTER(C.c_int), C.c_int, C.c_int, C.c_int, C.c_int] + [C.POINTER(C.c_int)] * 3
+lib.dau_mosaic_to_real.restype = C.c_int
 lib.dau_measure_fma_peak.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
 lib.dau_enable_timing.argtypes = [_vp, C.c_int]
 lib.dau_get_timing.argtypes = [_vp, C.c_int, _fp, C.c_int, C.POINTER(C.c_int)]

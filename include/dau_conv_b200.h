@@ -143,6 +143,14 @@ dau_status_t dau_train_step_host(dau_handle_t* h, int N, int S, int H, int W, in
                                  float* y_host, float* dx_host, float* dw_dev, float* dmu1_dev,
                                  float* dmu2_dev, float* dsigma_dev, void* stream);
 
+/* Host-side planning helpers (no device needed; used by the CPU test-suite).
+ * dau_plan_mosaic: how a batch of N narrow H x W images is packed into mosaic images for the
+ * 64-pixel-wide tiles of the kernels; out10 = {kx, ky, pitch_x, pitch_y, W, H, Wv, Hv, Nv, gap}.
+ * dau_mosaic_to_real: mosaic pixel (nv, vy, vx) -> real pixel; returns 1 and fills n/y/x for
+ * image pixels, 0 for gap pixels and for cells beyond the batch. */
+dau_status_t dau_plan_mosaic(int N, int H, int W, int gap, int* out10);
+int dau_mosaic_to_real(const int* mosaic10, int N, int nv, int vy, int vx, int* n, int* y, int* x);
+
 /* Measurement helpers used by bench.py (not part of the reference contract). */
 dau_status_t dau_measure_fma_peak(int device, int iters, double* tflops_out, double* ms_out);
 /* Per-kernel device times (ms) of the last forward / backward on this handle, measured with
