@@ -126,7 +126,7 @@ def run_reference(args, rank):
     if rank != 0:
         return
     N = CONFIGS[args.config][0]
-    n_sample = args.cpu_sample
+    n_sample = args.cpu_sample if args.cpu_sample > 0 else max(1, N // 4)
     value, ms, cores = time_cpu_reference(args.config, n_sample, args.steps, min(args.warmup, 1))
     sample = "%d of the %d images of the per-GPU batch per step (all other sizes unchanged)" % (n_sample, N)
     print(json.dumps({
@@ -282,10 +282,11 @@ def run_ours(args, rank, world, local_rank):
         return
     cpu_baseline = None
     if world == 1 and not args.no_cpu_baseline:
-        v, ms, cores = time_cpu_reference(args.config, args.cpu_sample, 1, 0)
+        n_cpu = args.cpu_sample if args.cpu_sample > 0 else N
+        v, ms, cores = time_cpu_reference(args.config, n_cpu, 1, 0)
         cpu_baseline = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                         "sample": "%d of the %d images of the batch, one fwd+bwd pass (%.1f s); oracle/dau_cpu.c, "
-                                  "C/OpenMP restatement of the reference CPU path" % (args.cpu_sample, N, ms / 1e3)}
+                                  "C/OpenMP restatement of the reference CPU path" % (n_cpu, N, ms / 1e3)}
     print(json.dumps({
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
@@ -309,7 +310,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="c2", choices=sorted(CONFIGS))
-    ap.add_argument("--cpu-sample", type=int, default=4, help="images per CPU-baseline pass")
+    ap.add_argument("--cpu-sample", type=int, default=0,
+                    help="images per CPU pass (0: the whole per-GPU batch for the cpu_baseline leg, about 10-15 s "
+                         "on C2; a quarter of it per step for --impl reference)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--e2e-chunk", type=int, default=16, help="images per chunk of the host-buffer step")
     args = ap.parse_args()

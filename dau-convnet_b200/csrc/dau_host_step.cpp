@@ -16,6 +16,7 @@
 #include "dau_host_step.hpp"
 
 #include <algorithm>
+#include <vector>
 
 namespace dau {
 
@@ -69,12 +70,24 @@ void HostPipeline::step(int N, int S, int H, int W, int chunk, float sigma_hint,
     const size_t in_img = (size_t)S * H * W, out_img = (size_t)F * H * W;
     auto up = [](size_t v) { return (v + 255) / 256 * 256; };
 
-    // plan the (at most two) chunk shapes and size the pool
+    // chunk schedule: short chunks at both ends (the first copy-in and the last copy-out are the
+    // only transfers nothing can hide), full chunks in between
+    std::vector<int> sizes;
+    {
+        const int q = chunk / 4, h = chunk / 2;
+        if (q >= 1 && N >= 2 * (q + h) + chunk) {
+            int mid = N - 2 * (q + h);
+            sizes.push_back(q); sizes.push_back(h);
+            while (mid > 0) { const int n = std::min(chunk, mid); sizes.push_back(n); mid -= n; }
+            sizes.push_back(h); sizes.push_back(q);
+        } else {
+            for (int left = N; left > 0; left -= chunk) sizes.push_back(std::min(chunk, left));
+        }
+    }
+    // plan every chunk shape and size the pool
     size_t fws = 0, bws = 0, ws_bytes = 0;
-    layer_for(chunk, S, H, W, sigma_hint, &fws, &bws);
-    ws_bytes = std::max(fws, bws);
-    if (N % chunk) {
-        layer_for(N % chunk, S, H, W, sigma_hint, &fws, &bws);
+    for (int n : sizes) {
+        layer_for(n, S, H, W, sigma_hint, &fws, &bws);
         ws_bytes = std::max(ws_bytes, std::max(fws, bws));
     }
     const size_t xin = up(chunk * in_img * 4), eout = up(chunk * out_img * 4);
@@ -104,8 +117,9 @@ void HostPipeline::step(int N, int S, int H, int W, int chunk, float sigma_hint,
 
     const unsigned flags = DAU_GRAD_W | DAU_GRAD_MU1 | DAU_GRAD_MU2 | DAU_GRAD_SIGMA | (dx ? DAU_GRAD_INPUT : 0u);
     int i = 0;
-    for (int n0 = 0; n0 < N; n0 += chunk, ++i) {
-        const int n = std::min(chunk, N - n0), b = i & 1;
+    size_t n0 = 0;
+    for (size_t ci = 0; ci < sizes.size(); n0 += sizes[ci], ++ci, ++i) {
+        const int n = sizes[ci], b = i & 1;
         DAUConvLayerB200* l = layer_for(n, S, H, W, sigma_hint, &fws, &bws);
         // copy-in: the buffers of chunk i-2 must have been consumed
         if (i >= 2) DAU_CUDA_CHECK(cudaStreamWaitEvent(s_in_, comp_done_[b], 0));
