@@ -180,30 +180,46 @@ def test_host_training_step_matches_device_path():
             close(got.cpu().numpy(), r, name, scale_atol=True)   # chunking reorders the fp32 sums
 
 
-def test_full_size_properties_config_c2():
-    """BASELINE config C2 (N=128, S=F=128, 64x64, G=4): size-independent identities.
-    (a) sum(E*Y) == sum_units w*dL/dw  (Y is linear in w; a checksum of all 3.4e10 unit-pixels)
-    (b) w=1, mu=0  =>  Y[:, f] == G * blur(sum_s X_s) for every f."""
+FULL_SIZE = {   # BASELINE.json configs at full size: (N, S, F, units, H, W, kernel_size, mu range)
+    "c2": (128, 128, 128, (2, 2), 64, 64, 9, 4.0),
+    "c4": (256, 512, 512, (1, 2), 28, 28, 17, 8.0),
+    "alexnet_l2": (256, 96, 256, (1, 2), 27, 27, 9, 3.0),
+    "alexnet_l4": (256, 384, 384, (1, 2), 13, 13, 9, 3.0),
+}
+
+
+@pytest.mark.parametrize("cfg", sorted(FULL_SIZE))
+def test_full_size_properties(cfg):
+    """BASELINE configs at FULL size (the oracle cannot run them): size-independent identities.
+    (a) sum(E*Y) == sum_units w*dL/dw  (Y is linear in w; a checksum over every unit-pixel)
+    (b) w=1, mu=0  =>  Y[:, f] == G * blur(sum_s X_s) for every f
+    (c) dL/dx is the adjoint of the forward map:  <E, Y(x)> == <dL/dx(E), x>."""
     import torch
     import dau_conv
     dev = torch.device("cuda:0")
-    N, S, F, G, H, W = 128, 128, 128, 4, 64, 64
+    N, S, F, units, H, W, ks, m = FULL_SIZE[cfg]
+    G = units[0] * units[1]
+    lim = ks // 2 - 0.01
     gen = torch.Generator(device=dev); gen.manual_seed(5)
     x = torch.rand((N, S, H, W), device=dev, generator=gen)
     e = torch.randn((N, F, H, W), device=dev, generator=gen)
     w = 0.1 * torch.randn((1, S, G, F), device=dev, generator=gen)
-    mu1 = (torch.rand((1, S, G, F), device=dev, generator=gen) * 8 - 4).clamp(-3.99, 3.99)
-    mu2 = (torch.rand((1, S, G, F), device=dev, generator=gen) * 8 - 4).clamp(-3.99, 3.99)
+    mu1 = (torch.rand((1, S, G, F), device=dev, generator=gen) * 2 * m - m).clamp(-lim, lim)
+    mu2 = (torch.rand((1, S, G, F), device=dev, generator=gen) * 2 * m - m).clamp(-lim, lim)
     sg = torch.full((1, S, G, F), 0.5, device=dev)
-    a = dict(num_output=F, number_units_x=2, number_units_y=2, kernel_size=9, pad=4)
+    a = dict(num_output=F, number_units_x=units[0], number_units_y=units[1], kernel_size=ks, pad=ks // 2)
     y = dau_conv.dau_conv_op(x, w, mu1, mu2, sg, **a)
     dx, dw, dm1, dm2, ds = dau_conv.dau_conv_grad_op(e, x, w, mu1, mu2, sg, **a)
     lhs = float((y.double() * e.double()).sum())
     rhs = float((w.double() * dw.double()).sum())
     scale = float((w.double() * dw.double()).abs().sum())
     assert abs(lhs - rhs) <= 1e-4 * abs(rhs) + 1e-6 * scale, (lhs, rhs, scale)
+    adj = float((dx.double() * x.double()).sum())                                    # (c)
+    scale_x = float((dx.double() * x.double()).abs().sum())
+    assert abs(lhs - adj) <= 1e-4 * abs(adj) + 1e-6 * scale_x, (lhs, adj, scale_x)
     for t in (dx, dm1, dm2, ds):
         assert bool(torch.isfinite(t).all())
+    del dx, dw, dm1, dm2, ds, y
     # (b)
     ones = torch.ones_like(w); zeros = torch.zeros_like(w)
     y1 = dau_conv.dau_conv_op(x, ones, zeros, zeros, sg, **a)

@@ -51,6 +51,11 @@ def main():
     ap.add_argument("--global-batch", type=int, default=256)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--overlap", type=int, default=1,
+                    help="1: gradient buckets are all-reduced while backward still runs (torch DDP); "
+                         "0: one all-reduce of all gradients after backward")
+    ap.add_argument("--graph", type=int, default=0,
+                    help="1: capture forward + backward + SGD of one rank in a CUDA graph (single GPU only)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -62,6 +67,10 @@ def main():
     torch.manual_seed(1234)                                    # identical parameters on every rank
     units = (1, 2) if args.variant == "default" else (2, 2)
     model = AlexNetDAU(units).to(dev)
+    net = model
+    if world > 1 and args.overlap:
+        net = nn.parallel.DistributedDataParallel(model, device_ids=[local], bucket_cap_mb=32,
+                                                  gradient_as_bucket_view=True)
     n_local = args.global_batch // world
     gen = torch.Generator(device=dev); gen.manual_seed(99 + rank)
     x = torch.rand((n_local, 3, 227, 227), device=dev, generator=gen)
@@ -72,9 +81,9 @@ def main():
 
     def step():
         opt.zero_grad(set_to_none=False)
-        loss = nn.functional.cross_entropy(model(x), target)
+        loss = nn.functional.cross_entropy(net(x), target)
         loss.backward()
-        if world > 1:                                          # one bucket: all gradients, summed, / world
+        if world > 1 and not args.overlap:                     # one bucket: all gradients, summed, / world
             flat = torch.cat([p.grad.reshape(-1) for p in params])
             dist.all_reduce(flat)
             flat /= world
@@ -93,6 +102,19 @@ def main():
     for _ in range(args.warmup):
         step()
     sync()
+    if args.graph and world == 1:
+        # everything in the step is stream-ordered and allocation-free after warm-up (the DAU op reads
+        # no device value on the host once sigma is known), so the whole step replays as one graph
+        graph = torch.cuda.CUDAGraph()
+        eager_step = step
+        with torch.cuda.graph(graph):
+            static_loss = eager_step()
+
+        def step():
+            graph.replay()
+            return static_loss
+        step()
+        sync()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(args.steps):
@@ -109,8 +131,10 @@ def main():
             "unit": "images/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
             "scaling": "strong", "dtype": "f32", "data": "synthetic", "loss": float(loss),
             "config": {"workload": "AlexNet-DAU-%s, %d DAU units, global batch %d at 227x227, batch-sharded dp%d, "
-                                   "one NCCL all-reduce of all gradients + SGD" % (
-                                       args.variant, n_dau_units, args.global_batch, world)}}))
+                                   "%s + SGD" % (
+                                       args.variant, n_dau_units, args.global_batch, world,
+                                       "bucketed NCCL all-reduce overlapped with backward" if args.overlap
+                                       else "one NCCL all-reduce of all gradients")}}))
     if world > 1:
         dist.destroy_process_group()
 
