@@ -192,8 +192,10 @@ FULL_SIZE = {   # BASELINE.json configs at full size: (N, S, F, units, H, W, ker
 def test_full_size_properties(cfg):
     """BASELINE configs at FULL size (the oracle cannot run them): size-independent identities.
     (a) sum(E*Y) == sum_units w*dL/dw  (Y is linear in w; a checksum over every unit-pixel)
-    (b) w=1, mu=0  =>  Y[:, f] == G * blur(sum_s X_s) for every f
-    (c) dL/dx is the adjoint of the forward map:  <E, Y(x)> == <dL/dx(E), x>."""
+    (b) w=1, mu=0  =>  Y[:, f] == G * blur(sum_s X_s) for every f.
+    (<E, Y(x)> == <dL/dx(E), x> is NOT an identity of the reference: it blurs the error first and
+    gathers second (base_dau_conv_layer.cu:278-325), which equals the adjoint only away from the
+    image border; dL/dx is pinned by the oracle tests instead.)"""
     import torch
     import dau_conv
     dev = torch.device("cuda:0")
@@ -214,9 +216,6 @@ def test_full_size_properties(cfg):
     rhs = float((w.double() * dw.double()).sum())
     scale = float((w.double() * dw.double()).abs().sum())
     assert abs(lhs - rhs) <= 1e-4 * abs(rhs) + 1e-6 * scale, (lhs, rhs, scale)
-    adj = float((dx.double() * x.double()).sum())                                    # (c)
-    scale_x = float((dx.double() * x.double()).abs().sum())
-    assert abs(lhs - adj) <= 1e-4 * abs(adj) + 1e-6 * scale_x, (lhs, adj, scale_x)
     for t in (dx, dm1, dm2, ds):
         assert bool(torch.isfinite(t).all())
     del dx, dw, dm1, dm2, ds, y
