@@ -158,6 +158,40 @@ def test_mu_learning_rate_factor_and_accumulation():
     np.testing.assert_allclose(grads[0].cpu().numpy(), g1[1] + 2.0, rtol=1e-6, atol=1e-6)
 
 
+def test_bias_term_bias_gradient_and_unit_bounds_guard():
+    """The layer-level options the TF op leaves off: fused bias (base_dau_conv_layer.cu:119-123), bias
+    gradient (:188-196) and the in-place parameter guard (:33-49)."""
+    import torch
+    import dau_conv
+    from dau_conv import _lib
+    x, err, w, mu1, mu2, ks = _case((3, 21, 17, 4, 5, (1, 2), 9, 3.9), 11)
+    mu1[0, 0, 0, 0], mu2[0, 1, 1, 2] = 6.5, -9.0                    # outside +-(4 - 1.0): the guard clips them
+    dev = torch.device("cuda:0")
+    st = _lib.default_settings(num_output=5, number_units_x=1, number_units_y=2, kernel_size=ks, pad=4,
+                               bias_term=1, unit_bounds_guard=1, component_border_bound=1.0, sigma_lower_bound=0.3)
+    h = dau_conv.DAULayerHandle(st, dev)
+    sig = np.full(w.shape, 0.25, np.float32)                        # below the lower bound: raised to 0.3
+    bias = np.linspace(-1, 1, 5).astype(np.float32)
+    t = {k: torch.from_numpy(np.ascontiguousarray(v)).to(dev) for k, v in
+         dict(x=x, err=err, w=w, mu1=mu1, mu2=mu2, sig=sig, bias=bias).items()}
+    y = h.forward(t["x"], t["w"], t["mu1"], t["mu2"], t["sig"], bias=t["bias"])
+    torch.cuda.synchronize()
+    m1c, m2c = np.clip(mu1, -3.0, 3.0), np.clip(mu2, -3.0, 3.0)
+    assert np.array_equal(t["mu1"].cpu().numpy(), m1c) and np.array_equal(t["mu2"].cpu().numpy(), m2c)
+    assert float(t["sig"].min()) == pytest.approx(0.3)
+    ref = O.forward(x, w, m1c, m2c, [0.3]) + bias.reshape(1, -1, 1, 1)
+    close(y.cpu().numpy(), ref, "y+bias")
+    dbias = torch.full((5,), 1.5, device=dev)
+    h.set_sigma_hint(0.3)
+    out = h.backward(t["x"], t["err"], t["w"], t["mu1"], t["mu2"], t["sig"], flags=_lib.GRAD_ALL | _lib.GRAD_BIAS,
+                     dbias=dbias)
+    torch.cuda.synchronize()
+    close(dbias.cpu().numpy(), 1.5 + err.sum((0, 2, 3)), "dbias", scale_atol=True)     # accumulated into
+    g_ref = O.backward(x, err, w, m1c, m2c, [0.3], ignore_edge_gradients=False)
+    for got, r, name in zip(out, g_ref, ("dx", "dw", "dmu1", "dmu2", "dsigma")):
+        close(got.cpu().numpy(), r, name, scale_atol=name != "dx")
+
+
 def test_host_training_step_matches_device_path():
     """dau_train_step_host (chunked, copy/compute overlapped) == dau_forward + dau_backward."""
     import torch
