@@ -7,253 +7,291 @@
 // rotated filter (:278-288).  out[y,x] = sum_{v,u} in[y+v-c, x+u-c] * fy[v]*fx[u], zero outside
 // the image.  Cost per pixel: (NH + NV)*Kb FMAs instead of NOUT*Kb^2.  Built for HBM speed:
 //
-//  * one CTA = one 64 x 32 output tile of one channel of an image PAIR: both images are filtered
-//    one after the other through the same shared-memory buffers and their results leave the SM
-//    together, because both consumer layouts interleave the two images of a pair
+//  * one CTA = one 64 x TH output tile of one channel of an image PAIR.  Both consumer layouts
+//    interleave the two images of a pair
 //        PG[n/2][c][y][x%4][x/4][n%2]                    (forward / dL/dx gather, dau_gather_tma.cu)
 //        XS[item][s][k][r<4][lane<32][c<2][img<2]        (parameter gradients, dau_grad_tma.cu)
-//    so every store is a full float2 / float4 and a warp's stores are contiguous;
-//  * a thread filters 4 consecutive pixels: the row pass reads 2*CQ+1 float4 from shared memory
-//    for 4 outputs, the column pass one float4 per tap (0.4 LDS wavefronts per pixel instead
-//    of 14 scalar loads), with the row filters pre-shifted on the host so that all register
-//    indices are static.
+//    so the two images travel through the kernel as the two halves of fma.rn.f32x2 operands:
+//    the row pass turns the two haloed input tiles into (img0, img1) float2 planes in shared
+//    memory, the column pass reads them with LDS.128 (2 pixels x 2 images), and every result
+//    leaves as a full float2 / float4 with a warp's stores contiguous;
+//  * the haloed tiles arrive by TMA (one cp.async.bulk.tensor.3d per image, zero fill outside the
+//    plane) when the planes are not a mosaic and rows are 16-byte multiples; mosaics and odd
+//    widths are staged element-wise with cp.async through the mosaic -> real mapping;
+//  * the filter half-width C is a template parameter: both passes are fully unrolled, taps come
+//    from the kernel parameter bank as (f, f) pairs, no zero taps are multiplied;
+//  * the column pass is register-blocked over RY output rows (2 for the bank, 4 for one
+//    filter), so a shared-memory row is read once for RY results.
 #include "dau_kernels.cuh"
+#include "dau_tma.cuh"
 
 namespace dau {
 
 namespace {
+using namespace tma;
+
 __device__ __forceinline__ void cp_async4_zfill(float* dst, const float* src, bool ok) {
     const unsigned d = (unsigned)__cvta_generic_to_shared(dst);
     const int sz = ok ? 4 : 0;
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;\n" ::"r"(d), "l"(src), "r"(sz) : "memory");
 }
-__device__ __forceinline__ void cp_async16_zfill(float* dst, const float* src, bool ok) {
-    const unsigned d = (unsigned)__cvta_generic_to_shared(dst);
-    const int sz = ok ? 16 : 0;
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(d), "l"(src), "r"(sz) : "memory");
+__device__ __forceinline__ void cp_async_commit_wait_all() {
+    asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;\n" ::: "memory");
 }
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
+// 3-D tiled tensor load global -> shared (dst 128-byte aligned); coordinates innermost first
+__device__ __forceinline__ void tensor3_g2s(void* dst, const CUtensorMap* map, int c0, int c1, int c2, uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];\n"
+        ::"r"(smem_u32(dst)), "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ float2 lo(const float4& v) { return make_float2(v.x, v.y); }
+__device__ __forceinline__ float2 hi(const float4& v) { return make_float2(v.z, v.w); }
 
-constexpr int PT_W = 64, PT_H = 32, PT_THREADS = 256;
+constexpr int PT_W = 64, PT_THREADS = 256;
 constexpr int PT_MAXTAPS = 17;
 
 struct PairBlurArgs {
-    float fx[3][PT_MAXTAPS];     // row filters, shifted: tap u' applies to tile column 4g + u' - 4*CQ
-    float fy[3][PT_MAXTAPS];     // column filters, tap v applies to row y + v - c
-    int kb, H, W, N, Cn, z0;     // H, W, N: mosaic extents
+    float2 fx[3][PT_MAXTAPS];    // row filters as (f, f): tap u applies to column x + u - c
+    float2 fy[3][PT_MAXTAPS];    // column filters as (f, f): tap v applies to row y + v - c
+    int H, W, N, Cn, z0;         // H, W, N: mosaic extents
     Mosaic m;                    // mosaic <-> real image mapping (identity for wide images)
     int tiles_x, tiles_y;        // XS: 64-column / 4-row item grid
     int qp, qv;                  // PG: padded / valid float2-columns per plane
 };
 
+template <int MODE, int C>
+struct TileGeom {
+    static constexpr int TH = MODE == 3 ? 16 : 32;           // output rows of a CTA
+    static constexpr int RY = MODE == 3 ? 2 : 4;             // output rows of a column-pass task
+    static constexpr int NH = MODE == 3 ? 3 : 1, NOUT = MODE == 3 ? 4 : 1;
+    static constexpr int CQ = (C + 3) / 4, PADX = 4 * CQ, SW = PT_W + 2 * PADX, NV = 2 * CQ + 1;
+    static constexpr int ROWS = TH + 2 * C, KB = 2 * C + 1;
+    static constexpr int IMG_FLOATS = (ROWS * SW + 31) / 32 * 32;     // a 128-byte multiple
+    static constexpr int PLANE4 = ROWS * 32;                 // float4 per (img0, img1) plane
+    static constexpr size_t SMEM = 128 + (size_t)2 * IMG_FLOATS * 4 + (size_t)NH * PLANE4 * 16 + 16;
+};
+
 // MODE 2: one filter -> PG.   MODE 3: derivative bank (h0,h1,h2 / v0,v1,v2) -> XS.
-template <int MODE, int CQ, bool IDENT>
-__global__ void __launch_bounds__(PT_THREADS)
-blur_pair_kernel(const float* __restrict__ in, float* __restrict__ out, const __grid_constant__ PairBlurArgs a) {
-    constexpr int NH = MODE == 3 ? 3 : 1, NOUT = MODE == 3 ? 4 : 1;
-    constexpr int PADX = 4 * CQ, NT = 8 * CQ + 1, SW = PT_W + 2 * PADX, NV = 2 * CQ + 1;
-    extern __shared__ float4 smem4[];
-    const int c = a.kb >> 1, rows = PT_H + 2 * c;
-    float* s_in0 = reinterpret_cast<float*>(smem4);         // [2 images][rows][SW]
-    float* s_h = s_in0 + 2 * rows * SW;                      // [NH][rows][PT_W]
+template <int MODE, int C, bool TMA>
+__global__ void __launch_bounds__(PT_THREADS, 4)
+blur_pair_kernel(const __grid_constant__ CUtensorMap in_map, const float* __restrict__ in, float* __restrict__ out,
+                 const __grid_constant__ PairBlurArgs a) {
+    using G = TileGeom<MODE, C>;
+    constexpr int TH = G::TH, RY = G::RY, NH = G::NH, NOUT = G::NOUT, PADX = G::PADX, SW = G::SW, NV = G::NV;
+    constexpr int ROWS = G::ROWS, KB = G::KB, IMG_FLOATS = G::IMG_FLOATS, PLANE4 = G::PLANE4;
+    extern __shared__ unsigned char smem_dyn[];
+    unsigned char* smem_raw = smem_dyn + ((128u - (smem_u32(smem_dyn) & 127u)) & 127u);
+    float* s_in = reinterpret_cast<float*>(smem_raw);                 // [2 images][ROWS][SW]
+    float4* s_h = reinterpret_cast<float4*>(s_in + 2 * IMG_FLOATS);   // [NH][ROWS][2 halves][16] (img0,img1) pairs
+    uint64_t* bar = reinterpret_cast<uint64_t*>(s_h + NH * PLANE4);
     const int tid = threadIdx.x;
-    const int x0 = blockIdx.x * PT_W, y0 = blockIdx.y * PT_H;
+    const int x0 = blockIdx.x * PT_W, y0 = blockIdx.y * TH;
     const int pc = a.z0 + blockIdx.z;                        // (pair, channel)
     const int np = pc / a.Cn, cn = pc - np * a.Cn;
     const int H = a.H, W = a.W;
-    constexpr bool ident = IDENT;
-    const size_t rplane = (size_t)a.m.H * a.m.W;
+    const bool ident = a.m.kx == 1 && a.m.ky == 1;
+    const bool live1 = 2 * np + 1 < a.N;
 
-    // ---- stage the haloed tiles of BOTH images with cp.async (zero fill outside the image): the
-    //      second image's HBM latency hides behind the first image's filtering --------------------
-    const bool vec16 = ident && (W & 3) == 0 && (reinterpret_cast<size_t>(in) & 15) == 0;
+    // ---- stage the haloed tiles of both images -----------------------------------------------------
+    if (TMA) {
+        if (tid == 0) {
+            mbar_init(bar, 1);
+            fence_barrier_init();
+            mbar_arrive_expect_tx(bar, (live1 ? 2u : 1u) * ROWS * SW * 4u);
+            tensor3_g2s(s_in, &in_map, x0 - PADX, y0 - C, (2 * np) * a.Cn + cn, bar);
+            if (live1) tensor3_g2s(s_in + IMG_FLOATS, &in_map, x0 - PADX, y0 - C, (2 * np + 1) * a.Cn + cn, bar);
+        }
+        if (!live1)
+            for (int i = tid; i < ROWS * SW; i += PT_THREADS) s_in[IMG_FLOATS + i] = 0.f;
+        __syncthreads();                                     // barrier initialised (and zeros visible)
+        mbar_wait(bar, 0);
+    } else {
+        const size_t rplane = (size_t)a.m.H * a.m.W;
 #pragma unroll
-    for (int img = 0; img < 2; ++img) {
-        const int n = 2 * np + img;                          // mosaic image
-        const bool live = n < a.N;
-        float* dst = s_in0 + img * rows * SW;
-        if (vec16) {
-            const float* src = in + ((size_t)n * a.Cn + cn) * rplane;
-            for (int i = tid; i < rows * (SW / 4); i += PT_THREADS) {
-                const int r = i / (SW / 4), q = (i - r * (SW / 4)) * 4;
-                const int gy = y0 + r - c, gx = x0 + q - PADX;       // gx % 4 == 0: all in or all out
-                const bool ok = live && gy >= 0 && gy < H && gx >= 0 && gx < W;
-                cp_async16_zfill(dst + r * SW + q, ok ? src + (size_t)gy * W + gx : in, ok);
-            }
-        } else {
-            for (int i = tid; i < rows * SW; i += PT_THREADS) {
+        for (int img = 0; img < 2; ++img) {
+            const int n = 2 * np + img;                      // mosaic image
+            float* dst = s_in + img * IMG_FLOATS;
+            for (int i = tid; i < ROWS * SW; i += PT_THREADS) {
                 const int r = i / SW, q = i - r * SW;
-                const int gy = y0 + r - c, gx = x0 + q - PADX;
+                const int gy = y0 + r - C, gx = x0 + q - PADX;
                 const float* src = in;
-                bool ok = live && gy >= 0 && gy < H && gx >= 0 && gx < W;
+                bool ok = n < a.N && gy >= 0 && gy < H && gx >= 0 && gx < W;
                 if (ok) {
-                    if (ident) {
-                        src = in + ((size_t)n * a.Cn + cn) * rplane + (size_t)gy * W + gx;
-                    } else {
-                        int rn, ry, rx;
-                        ok = mosaic_to_real(a.m, n, gy, gx, &rn, &ry, &rx);
-                        if (ok) src = in + ((size_t)rn * a.Cn + cn) * rplane + (size_t)ry * a.m.W + rx;
-                    }
+                    int rn = n, ry = gy, rx = gx;
+                    if (!ident) ok = mosaic_to_real(a.m, n, gy, gx, &rn, &ry, &rx);
+                    if (ok) src = in + ((size_t)rn * a.Cn + cn) * rplane + (size_t)ry * a.m.W + rx;
                 }
                 cp_async4_zfill(dst + i, src, ok);
             }
         }
-        cp_async_commit();
+        cp_async_commit_wait_all();
+        __syncthreads();
     }
 
-    float4 res[2][2][NOUT];
+    // ---- row pass: 4 pixels of both images per task, results stored as (img0, img1) pairs.  Scalar
+    //      FMAs: the two images arrive in separate registers, and pairing them for f32x2 costs more
+    //      moves than it saves ------------------------------------------------------------------------
+    for (int t = tid; t < ROWS * 16; t += PT_THREADS) {
+        const int r = t >> 4, g = t & 15;
+        const float4* sp0 = reinterpret_cast<const float4*>(s_in + r * SW + 4 * g);
+        const float4* sp1 = reinterpret_cast<const float4*>(s_in + IMG_FLOATS + r * SW + 4 * g);
+        float x0v[4 * NV], x1v[4 * NV];
 #pragma unroll
-    for (int img = 0; img < 2; ++img) {
-        const int n = 2 * np + img;
-        const bool live = n < a.N;
-        const float* s_in = s_in0 + img * rows * SW;
-        if (img == 0) cp_async_wait<1>(); else cp_async_wait<0>();
-        __syncthreads();
-        // ---- row pass: 4 outputs per task --------------------------------------------------------
-        for (int t = tid; t < rows * (PT_W / 4); t += PT_THREADS) {
-            const int r = t >> 4, g = t & 15;
-            float xin[4 * NV];
-            const float4* sp = reinterpret_cast<const float4*>(s_in + r * SW + 4 * g);
-#pragma unroll
-            for (int j = 0; j < NV; ++j) {
-                const float4 v = sp[j];
-                xin[4 * j] = v.x; xin[4 * j + 1] = v.y; xin[4 * j + 2] = v.z; xin[4 * j + 3] = v.w;
-            }
-#pragma unroll
-            for (int j = 0; j < NH; ++j) {
-                float4 h = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-                for (int u = 0; u < NT; ++u) {
-                    const float f = a.fx[j][u];
-                    h.x = fmaf(xin[u], f, h.x); h.y = fmaf(xin[u + 1], f, h.y);
-                    h.z = fmaf(xin[u + 2], f, h.z); h.w = fmaf(xin[u + 3], f, h.w);
-                }
-                *reinterpret_cast<float4*>(s_h + (j * rows + r) * PT_W + 4 * g) = h;
-            }
+        for (int j = 0; j < NV; ++j) {
+            const float4 v0 = sp0[j], v1 = sp1[j];
+            x0v[4 * j] = v0.x; x0v[4 * j + 1] = v0.y; x0v[4 * j + 2] = v0.z; x0v[4 * j + 3] = v0.w;
+            x1v[4 * j] = v1.x; x1v[4 * j + 1] = v1.y; x1v[4 * j + 2] = v1.z; x1v[4 * j + 3] = v1.w;
         }
-        __syncthreads();
-        // ---- column pass: 2 tasks of 4 outputs per thread ---------------------------------------
 #pragma unroll
-        for (int tt = 0; tt < 2; ++tt) {
-            const int t = tid + tt * PT_THREADS;
-            const int y = t >> 4, g = t & 15;
-            const float4* hp = reinterpret_cast<const float4*>(s_h + y * PT_W + 4 * g);
-            const int hs = rows * PT_W / 4;                  // float4 stride between the NH planes
-            float4 o[NOUT];
-#pragma unroll
-            for (int k = 0; k < NOUT; ++k) o[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-            for (int v = 0; v < a.kb; ++v) {
-                const float4 t0 = hp[v * (PT_W / 4)];
-                if (MODE == 3) {
-                    const float4 t1 = hp[hs + v * (PT_W / 4)], t2 = hp[2 * hs + v * (PT_W / 4)];
-                    const float v0 = a.fy[0][v], v1 = a.fy[1][v], v2 = a.fy[2][v];
-                    // X_w = v0[h0]   X_mu1 = v0[h1]   X_mu2 = v1[h0]   X_sigma = v0[h2] + v2[h0]
-                    o[0].x = fmaf(t0.x, v0, o[0].x); o[0].y = fmaf(t0.y, v0, o[0].y);
-                    o[0].z = fmaf(t0.z, v0, o[0].z); o[0].w = fmaf(t0.w, v0, o[0].w);
-                    o[1 % NOUT].x = fmaf(t1.x, v0, o[1 % NOUT].x); o[1 % NOUT].y = fmaf(t1.y, v0, o[1 % NOUT].y);
-                    o[1 % NOUT].z = fmaf(t1.z, v0, o[1 % NOUT].z); o[1 % NOUT].w = fmaf(t1.w, v0, o[1 % NOUT].w);
-                    o[2 % NOUT].x = fmaf(t0.x, v1, o[2 % NOUT].x); o[2 % NOUT].y = fmaf(t0.y, v1, o[2 % NOUT].y);
-                    o[2 % NOUT].z = fmaf(t0.z, v1, o[2 % NOUT].z); o[2 % NOUT].w = fmaf(t0.w, v1, o[2 % NOUT].w);
-                    o[3 % NOUT].x = fmaf(t2.x, v0, o[3 % NOUT].x); o[3 % NOUT].y = fmaf(t2.y, v0, o[3 % NOUT].y);
-                    o[3 % NOUT].z = fmaf(t2.z, v0, o[3 % NOUT].z); o[3 % NOUT].w = fmaf(t2.w, v0, o[3 % NOUT].w);
-                    o[3 % NOUT].x = fmaf(t0.x, v2, o[3 % NOUT].x); o[3 % NOUT].y = fmaf(t0.y, v2, o[3 % NOUT].y);
-                    o[3 % NOUT].z = fmaf(t0.z, v2, o[3 % NOUT].z); o[3 % NOUT].w = fmaf(t0.w, v2, o[3 % NOUT].w);
-                } else {
-                    const float v0 = a.fy[0][v];
-                    o[0].x = fmaf(t0.x, v0, o[0].x); o[0].y = fmaf(t0.y, v0, o[0].y);
-                    o[0].z = fmaf(t0.z, v0, o[0].z); o[0].w = fmaf(t0.w, v0, o[0].w);
-                }
-            }
-            // zero what lies outside the image (pad columns / rows of the consumer layouts)
-            const int gy = y0 + y, gx = x0 + 4 * g;
-            const bool rowok = live && gy < H;
-            bool ok[4];
+        for (int j = 0; j < NH; ++j) {
+            float h0[4], h1[4];
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
-                ok[i] = rowok && gx + i < W;
-                if (ok[i] && !ident) {                       // blur tails inside the gaps are not image
-                    int rn, ry, rx;
-                    ok[i] = mosaic_to_real(a.m, n, gy, gx + i, &rn, &ry, &rx);
+                h0[i] = x0v[PADX - C + i] * a.fx[j][0].x;
+                h1[i] = x1v[PADX - C + i] * a.fx[j][0].x;
+            }
+#pragma unroll
+            for (int u = 1; u < KB; ++u) {
+                const float f = a.fx[j][u].x;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    h0[i] = fmaf(x0v[u + PADX - C + i], f, h0[i]);
+                    h1[i] = fmaf(x1v[u + PADX - C + i], f, h1[i]);
                 }
             }
+            float4* hp = s_h + j * PLANE4 + r * 32 + g;
+            hp[0] = make_float4(h0[0], h1[0], h0[1], h1[1]);
+            hp[16] = make_float4(h0[2], h1[2], h0[3], h1[3]);
+        }
+    }
+    __syncthreads();
+
+    // ---- column pass: a warp = RY output rows x 64 columns x 2 images; lane = (half p, group g) ----
+    const int warp = tid >> 5, lane = tid & 31, p = lane >> 4, g = lane & 15;
+    const int gx = x0 + 4 * g + 2 * p;                       // first of the lane's two pixels
+    const bool interior = ident && live1 && x0 + PT_W <= W && y0 + TH <= H;
+    for (int yb = warp; yb < TH / RY; yb += PT_THREADS / 32) {
+        float2 acc[RY][NOUT][2];
 #pragma unroll
-            for (int k = 0; k < NOUT; ++k) {
-                if (!ok[0]) o[k].x = 0.f;
-                if (!ok[1]) o[k].y = 0.f;
-                if (!ok[2]) o[k].z = 0.f;
-                if (!ok[3]) o[k].w = 0.f;
-                res[img][tt][k] = o[k];
+        for (int o = 0; o < RY; ++o)
+#pragma unroll
+            for (int k = 0; k < NOUT; ++k) acc[o][k][0] = acc[o][k][1] = make_float2(0.f, 0.f);
+        const float4* hp = s_h + (yb * RY) * 32 + p * 16 + g;
+#pragma unroll
+        for (int i = 0; i < KB + RY - 1; ++i) {              // input row yb*RY + i of the haloed tile
+            const float4 t0 = hp[i * 32];
+            float4 t1 = t0, t2 = t0;
+            if (MODE == 3) { t1 = hp[PLANE4 + i * 32]; t2 = hp[2 * PLANE4 + i * 32]; }
+#pragma unroll
+            for (int o = 0; o < RY; ++o) {
+                const int v = i - o;                         // tap of output row o
+                if (v < 0 || v >= KB) continue;
+                const float2 v0 = a.fy[0][v];
+                acc[o][0][0] = __ffma2_rn(lo(t0), v0, acc[o][0][0]);
+                acc[o][0][1] = __ffma2_rn(hi(t0), v0, acc[o][0][1]);
+                if (MODE == 3) {
+                    // X_w = v0[h0]   X_mu1 = v0[h1]   X_mu2 = v1[h0]   X_sigma = v0[h2] + v2[h0]
+                    const float2 v1 = a.fy[1][v], v2 = a.fy[2][v];
+                    acc[o][1 % NOUT][0] = __ffma2_rn(lo(t1), v0, acc[o][1 % NOUT][0]);
+                    acc[o][1 % NOUT][1] = __ffma2_rn(hi(t1), v0, acc[o][1 % NOUT][1]);
+                    acc[o][2 % NOUT][0] = __ffma2_rn(lo(t0), v1, acc[o][2 % NOUT][0]);
+                    acc[o][2 % NOUT][1] = __ffma2_rn(hi(t0), v1, acc[o][2 % NOUT][1]);
+                    acc[o][3 % NOUT][0] = __ffma2_rn(lo(t2), v0, acc[o][3 % NOUT][0]);
+                    acc[o][3 % NOUT][1] = __ffma2_rn(hi(t2), v0, acc[o][3 % NOUT][1]);
+                    acc[o][3 % NOUT][0] = __ffma2_rn(lo(t0), v2, acc[o][3 % NOUT][0]);
+                    acc[o][3 % NOUT][1] = __ffma2_rn(hi(t0), v2, acc[o][3 % NOUT][1]);
+                }
             }
         }
-        __syncthreads();                                     // the next image re-uses both buffers
-    }
-
-    // ---- both images leave together --------------------------------------------------------------
 #pragma unroll
-    for (int tt = 0; tt < 2; ++tt) {
-        const int t = tid + tt * PT_THREADS;
-        const int y = t >> 4, g = t & 15;
-        const int gy = y0 + y, gx = x0 + 4 * g;
-        if (MODE == 2) {
-            const int q = gx >> 2;
-            if (gy >= H || q >= a.qv) continue;
-            float2* o = reinterpret_cast<float2*>(out) + (((size_t)pc * H + gy) * 4) * a.qp + q;
-            const float4 r0 = res[0][tt][0], r1 = res[1][tt][0];
-            o[0] = make_float2(r0.x, r1.x);
-            o[a.qp] = make_float2(r0.y, r1.y);
-            o[2 * a.qp] = make_float2(r0.z, r1.z);
-            o[3 * a.qp] = make_float2(r0.w, r1.w);
-        } else {
-            if (gy >= a.tiles_y * 4 || gx >= a.tiles_x * 64) continue;
-            const size_t item = ((size_t)np * a.tiles_y + (gy >> 2)) * a.tiles_x + (gx >> 6);
-            float4* o = reinterpret_cast<float4*>(out + ((item * a.Cn + cn) * 16 + (gy & 3)) * 128 + (gx & 63) * 2);
+        for (int o = 0; o < RY; ++o) {
+            const int gy = y0 + yb * RY + o;
+            if (!interior) {
+                // zero what lies outside the image: pad columns / rows of the consumer layouts, the
+                // second image of an odd batch, blur tails inside the mosaic gaps
 #pragma unroll
-            for (int k = 0; k < NOUT; ++k) {
-                const float4 r0 = res[0][tt][k], r1 = res[1][tt][k];
-                o[k * 128] = make_float4(r0.x, r1.x, r0.y, r1.y);          // k stride: 4 rows * 128 floats
-                o[k * 128 + 1] = make_float4(r0.z, r1.z, r0.w, r1.w);
+                for (int i = 0; i < 2; ++i) {
+                    bool ok0 = gy < H && gx + i < W, ok1 = ok0 && live1;
+                    if (ok0 && !ident) {
+                        int rn, ry, rx;
+                        ok0 = mosaic_to_real(a.m, 2 * np, gy, gx + i, &rn, &ry, &rx);
+                        ok1 = ok1 && mosaic_to_real(a.m, 2 * np + 1, gy, gx + i, &rn, &ry, &rx);
+                    }
+#pragma unroll
+                    for (int k = 0; k < NOUT; ++k) {
+                        if (!ok0) acc[o][k][i].x = 0.f;
+                        if (!ok1) acc[o][k][i].y = 0.f;
+                    }
+                }
+            }
+            if (MODE == 2) {
+                const int q = (x0 >> 2) + g;
+                if (gy >= H || q >= a.qv) continue;
+                float2* o2 = reinterpret_cast<float2*>(out) + (((size_t)pc * H + gy) * 4 + 2 * p) * a.qp + q;
+                o2[0] = acc[o][0][0];
+                o2[a.qp] = acc[o][0][1];
+            } else {
+                if (gy >= a.tiles_y * 4) continue;
+                const size_t item = ((size_t)np * a.tiles_y + (gy >> 2)) * a.tiles_x + blockIdx.x;
+                float4* o4 = reinterpret_cast<float4*>(out + ((item * a.Cn + cn) * 16 + (gy & 3)) * 128) + 2 * g + p;
+#pragma unroll
+                for (int k = 0; k < NOUT; ++k)               // k stride: 4 rows * 128 floats
+                    o4[k * 128] = make_float4(acc[o][k][0].x, acc[o][k][0].y, acc[o][k][1].x, acc[o][k][1].y);
             }
         }
     }
 }
 
-int cq_of(int kb) { const int cq = ((kb >> 1) + 3) / 4; return cq < 1 ? 1 : cq; }
-
-void fill_row_filter(float* dst, const float* f, int kb, int cq) {
-    // tap u' <-> tile column offset u' - 4*cq; the filter's tap u sits at offset u - c
-    const int c = kb >> 1, shift = 4 * cq - c;
-    for (int i = 0; i < PT_MAXTAPS; ++i) dst[i] = 0.f;
-    for (int u = 0; u < kb; ++u) dst[u + shift] = f[u];
-}
-
-template <int MODE>
-void launch_pair(const float* in, float* out, PairBlurArgs& a, int pairs_times_c, cudaStream_t stream) {
-    const int c = a.kb >> 1, cq = cq_of(a.kb);
-    const int rows = PT_H + 2 * c, sw = PT_W + 8 * cq, nh = MODE == 3 ? 3 : 1;
-    const size_t smem = (size_t)(2 * rows * sw + nh * rows * PT_W) * sizeof(float);
+template <int MODE, int C>
+void launch_c(const float* in, float* out, PairBlurArgs& a, int pairs_times_c, cudaStream_t stream) {
+    using G = TileGeom<MODE, C>;
+    const bool ident = a.m.kx == 1 && a.m.ky == 1;
+    // TMA needs 16-byte row pitch and base; everything else goes through the element-wise path
+    const bool use_tma = ident && (a.W & 3) == 0 && (reinterpret_cast<size_t>(in) & 15) == 0;
     static bool attr_set = false;
     if (!attr_set) {
-        DAU_CUDA_CHECK(cudaFuncSetAttribute(blur_pair_kernel<MODE, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
-        DAU_CUDA_CHECK(cudaFuncSetAttribute(blur_pair_kernel<MODE, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
-        DAU_CUDA_CHECK(cudaFuncSetAttribute(blur_pair_kernel<MODE, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
-        DAU_CUDA_CHECK(cudaFuncSetAttribute(blur_pair_kernel<MODE, 2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+        DAU_CUDA_CHECK(cudaFuncSetAttribute(blur_pair_kernel<MODE, C, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::SMEM));
+        DAU_CUDA_CHECK(cudaFuncSetAttribute(blur_pair_kernel<MODE, C, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::SMEM));
         attr_set = true;
     }
+    CUtensorMap map;
+    memset(&map, 0, sizeof(map));
+    if (use_tma) {
+        const uint64_t dims[3] = {(uint64_t)a.W, (uint64_t)a.H, (uint64_t)a.N * a.Cn};
+        const uint64_t strides[2] = {(uint64_t)a.W * 4, (uint64_t)a.H * a.W * 4};
+        const uint32_t box[3] = {(uint32_t)G::SW, (uint32_t)G::ROWS, 1};
+        map = make_map_f32(in, 3, dims, strides, box);
+    }
     const int gx = MODE == 3 ? a.tiles_x : (a.W + PT_W - 1) / PT_W;
-    const int gy = MODE == 3 ? (a.tiles_y * 4 + PT_H - 1) / PT_H : (a.H + PT_H - 1) / PT_H;
+    const int gy = MODE == 3 ? (a.tiles_y * 4 + G::TH - 1) / G::TH : (a.H + G::TH - 1) / G::TH;
     for (int z0 = 0; z0 < pairs_times_c; z0 += 65535) {
         const int nz = pairs_times_c - z0 < 65535 ? pairs_times_c - z0 : 65535;
         a.z0 = z0;
-        const bool ident = a.m.kx == 1 && a.m.ky == 1;
         const dim3 grid(gx, gy, nz);
-        if (cq == 1 && ident) blur_pair_kernel<MODE, 1, true><<<grid, PT_THREADS, smem, stream>>>(in, out, a);
-        else if (cq == 1) blur_pair_kernel<MODE, 1, false><<<grid, PT_THREADS, smem, stream>>>(in, out, a);
-        else if (ident) blur_pair_kernel<MODE, 2, true><<<grid, PT_THREADS, smem, stream>>>(in, out, a);
-        else blur_pair_kernel<MODE, 2, false><<<grid, PT_THREADS, smem, stream>>>(in, out, a);
+        if (use_tma) blur_pair_kernel<MODE, C, true><<<grid, PT_THREADS, G::SMEM, stream>>>(map, in, out, a);
+        else blur_pair_kernel<MODE, C, false><<<grid, PT_THREADS, G::SMEM, stream>>>(map, in, out, a);
     }
     DAU_CUDA_CHECK(cudaGetLastError());
+}
+
+template <int MODE>
+void launch_pair(const float* in, float* out, PairBlurArgs& a, int kb, int pairs_times_c, cudaStream_t stream) {
+    switch (kb >> 1) {
+        case 1: launch_c<MODE, 1>(in, out, a, pairs_times_c, stream); break;
+        case 2: launch_c<MODE, 2>(in, out, a, pairs_times_c, stream); break;
+        case 3: launch_c<MODE, 3>(in, out, a, pairs_times_c, stream); break;
+        case 4: launch_c<MODE, 4>(in, out, a, pairs_times_c, stream); break;
+        case 5: launch_c<MODE, 5>(in, out, a, pairs_times_c, stream); break;
+        case 6: launch_c<MODE, 6>(in, out, a, pairs_times_c, stream); break;
+        case 7: launch_c<MODE, 7>(in, out, a, pairs_times_c, stream); break;
+        case 8: launch_c<MODE, 8>(in, out, a, pairs_times_c, stream); break;
+        default: DAU_CHECK(false, 1, "blur kernel size must be odd, >= 3 and <= 17");
+    }
+}
+
+void fill_pairs(float2* dst, const float* f, int kb) {
+    for (int i = 0; i < PT_MAXTAPS; ++i) dst[i] = make_float2(0.f, 0.f);
+    for (int i = 0; i < kb; ++i) dst[i] = make_float2(f[i], f[i]);
 }
 }  // namespace
 
@@ -262,13 +300,13 @@ void launch_blur_single_paired(const float* in, float* out_paired, const Mosaic&
     const int N = m.Nv, H = m.Hv, W = m.Wv;
     DAU_CHECK(m.gap >= (kb >> 1) || (m.kx == 1 && m.ky == 1), 4,
               "blur wider than the mosaic gap: call dau_set_sigma_hint before dau_reshape");
-    DAU_CHECK(kb >= 1 && kb <= PT_MAXTAPS && (kb & 1), 1, "blur kernel size must be odd and <= 17");
+    DAU_CHECK(kb >= 3 && kb <= PT_MAXTAPS && (kb & 1), 1, "blur kernel size must be odd, >= 3 and <= 17");
     PairBlurArgs a; memset(&a, 0, sizeof(a));
-    fill_row_filter(a.fx[0], fx, kb, cq_of(kb));
-    for (int i = 0; i < kb; ++i) a.fy[0][i] = fy[i];
-    a.kb = kb; a.H = H; a.W = W; a.N = N; a.Cn = Cn; a.m = m;
+    fill_pairs(a.fx[0], fx, kb);
+    fill_pairs(a.fy[0], fy, kb);
+    a.H = H; a.W = W; a.N = N; a.Cn = Cn; a.m = m;
     a.qv = (W + 3) / 4; a.qp = (a.qv + 1) / 2 * 2;
-    launch_pair<2>(in, out_paired, a, ((N + 1) / 2) * Cn, stream);
+    launch_pair<2>(in, out_paired, a, kb, ((N + 1) / 2) * Cn, stream);
 }
 
 void launch_blur_bank_strips(const float* in, float* out_strips, const Mosaic& m, int S,
@@ -276,16 +314,13 @@ void launch_blur_bank_strips(const float* in, float* out_strips, const Mosaic& m
     const int N = m.Nv, H = m.Hv, W = m.Wv;
     DAU_CHECK(m.gap >= (f.kb >> 1) || (m.kx == 1 && m.ky == 1), 4,
               "blur wider than the mosaic gap: call dau_set_sigma_hint before dau_reshape");
-    DAU_CHECK(f.kb >= 1 && f.kb <= PT_MAXTAPS && (f.kb & 1), 1, "blur kernel size must be odd and <= 17");
+    DAU_CHECK(f.kb >= 3 && f.kb <= PT_MAXTAPS && (f.kb & 1), 1, "blur kernel size must be odd, >= 3 and <= 17");
     PairBlurArgs a; memset(&a, 0, sizeof(a));
-    const int cq = cq_of(f.kb);
-    fill_row_filter(a.fx[0], f.h0, f.kb, cq);
-    fill_row_filter(a.fx[1], f.h1, f.kb, cq);
-    fill_row_filter(a.fx[2], f.h2, f.kb, cq);
-    for (int i = 0; i < f.kb; ++i) { a.fy[0][i] = f.v0[i]; a.fy[1][i] = f.v1[i]; a.fy[2][i] = f.v2[i]; }
-    a.kb = f.kb; a.H = H; a.W = W; a.N = N; a.Cn = S; a.m = m;
+    fill_pairs(a.fx[0], f.h0, f.kb); fill_pairs(a.fx[1], f.h1, f.kb); fill_pairs(a.fx[2], f.h2, f.kb);
+    fill_pairs(a.fy[0], f.v0, f.kb); fill_pairs(a.fy[1], f.v1, f.kb); fill_pairs(a.fy[2], f.v2, f.kb);
+    a.H = H; a.W = W; a.N = N; a.Cn = S; a.m = m;
     a.tiles_x = (W + 63) / 64; a.tiles_y = (H + 3) / 4;
-    launch_pair<3>(in, out_strips, a, ((N + 1) / 2) * S, stream);
+    launch_pair<3>(in, out_strips, a, f.kb, ((N + 1) / 2) * S, stream);
 }
 
 }  // namespace dau
