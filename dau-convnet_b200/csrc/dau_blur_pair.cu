@@ -57,6 +57,11 @@ struct PairBlurArgs {
     Mosaic m;                    // mosaic <-> real image mapping (identity for wide images)
     int tiles_x, tiles_y;        // XS: 64-column / 4-row item grid
     int qp, qv;                  // PG: padded / valid float2-columns per plane
+    // MODE 2 extras (the top error on its way into the backward pass):
+    const float* mask;           // same shape as `in`: in[i] is taken as 0 where mask[i] <= 0 (ReLU backward)
+    float2* sgp;                 // also emit the (masked) input as SGP[n/2][c][y][x%2][x/2][n%2] for the gradient kernel
+    int sgp_qp;                  // padded float2-columns per SGP plane
+    int edge_row, edge_col;      // ignore_edge_gradients: SGP gets zeros in the last real row / column
 };
 
 template <int MODE, int C>
@@ -68,14 +73,15 @@ struct TileGeom {
     static constexpr int ROWS = TH + 2 * C, KB = 2 * C + 1;
     static constexpr int IMG_FLOATS = (ROWS * SW + 31) / 32 * 32;     // a 128-byte multiple
     static constexpr int PLANE4 = ROWS * 32;                 // float4 per (img0, img1) plane
-    static constexpr size_t SMEM = 128 + (size_t)2 * IMG_FLOATS * 4 + (size_t)NH * PLANE4 * 16 + 16;
+    static constexpr size_t SMEM = 128 + (size_t)2 * IMG_FLOATS * 4 + (size_t)NH * PLANE4 * 16 + 128;
+    static constexpr size_t SMEM_MASK = (size_t)2 * IMG_FLOATS * 4;   // extra bytes when a mask is staged
 };
 
 // MODE 2: one filter -> PG.   MODE 3: derivative bank (h0,h1,h2 / v0,v1,v2) -> XS.
 template <int MODE, int C, bool TMA>
 __global__ void __launch_bounds__(PT_THREADS, 4)
-blur_pair_kernel(const __grid_constant__ CUtensorMap in_map, const float* __restrict__ in, float* __restrict__ out,
-                 const __grid_constant__ PairBlurArgs a) {
+blur_pair_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constant__ CUtensorMap mask_map,
+                 const float* __restrict__ in, float* __restrict__ out, const __grid_constant__ PairBlurArgs a) {
     using G = TileGeom<MODE, C>;
     constexpr int TH = G::TH, RY = G::RY, NH = G::NH, NOUT = G::NOUT, PADX = G::PADX, SW = G::SW, NV = G::NV;
     constexpr int ROWS = G::ROWS, KB = G::KB, IMG_FLOATS = G::IMG_FLOATS, PLANE4 = G::PLANE4;
@@ -84,6 +90,8 @@ blur_pair_kernel(const __grid_constant__ CUtensorMap in_map, const float* __rest
     float* s_in = reinterpret_cast<float*>(smem_raw);                 // [2 images][ROWS][SW]
     float4* s_h = reinterpret_cast<float4*>(s_in + 2 * IMG_FLOATS);   // [NH][ROWS][2 halves][16] (img0,img1) pairs
     uint64_t* bar = reinterpret_cast<uint64_t*>(s_h + NH * PLANE4);
+    float* s_mask = reinterpret_cast<float*>(bar + 16);              // [2 images][ROWS][SW], only with a.mask
+    const bool masked = MODE == 2 && a.mask != nullptr;
     const int tid = threadIdx.x;
     const int x0 = blockIdx.x * PT_W, y0 = blockIdx.y * TH;
     const int pc = a.z0 + blockIdx.z;                        // (pair, channel)
@@ -97,12 +105,19 @@ blur_pair_kernel(const __grid_constant__ CUtensorMap in_map, const float* __rest
         if (tid == 0) {
             mbar_init(bar, 1);
             fence_barrier_init();
-            mbar_arrive_expect_tx(bar, (live1 ? 2u : 1u) * ROWS * SW * 4u);
+            mbar_arrive_expect_tx(bar, (live1 ? 2u : 1u) * (masked ? 2u : 1u) * ROWS * SW * 4u);
             tensor3_g2s(s_in, &in_map, x0 - PADX, y0 - C, (2 * np) * a.Cn + cn, bar);
             if (live1) tensor3_g2s(s_in + IMG_FLOATS, &in_map, x0 - PADX, y0 - C, (2 * np + 1) * a.Cn + cn, bar);
+            if (masked) {
+                tensor3_g2s(s_mask, &mask_map, x0 - PADX, y0 - C, (2 * np) * a.Cn + cn, bar);
+                if (live1) tensor3_g2s(s_mask + IMG_FLOATS, &mask_map, x0 - PADX, y0 - C, (2 * np + 1) * a.Cn + cn, bar);
+            }
         }
         if (!live1)
-            for (int i = tid; i < ROWS * SW; i += PT_THREADS) s_in[IMG_FLOATS + i] = 0.f;
+            for (int i = tid; i < ROWS * SW; i += PT_THREADS) {
+                s_in[IMG_FLOATS + i] = 0.f;
+                if (masked) s_mask[IMG_FLOATS + i] = 0.f;
+            }
         __syncthreads();                                     // barrier initialised (and zeros visible)
         mbar_wait(bar, 0);
     } else {
@@ -114,18 +129,58 @@ blur_pair_kernel(const __grid_constant__ CUtensorMap in_map, const float* __rest
             for (int i = tid; i < ROWS * SW; i += PT_THREADS) {
                 const int r = i / SW, q = i - r * SW;
                 const int gy = y0 + r - C, gx = x0 + q - PADX;
-                const float* src = in;
+                size_t src = 0;
                 bool ok = n < a.N && gy >= 0 && gy < H && gx >= 0 && gx < W;
                 if (ok) {
                     int rn = n, ry = gy, rx = gx;
                     if (!ident) ok = mosaic_to_real(a.m, n, gy, gx, &rn, &ry, &rx);
-                    if (ok) src = in + ((size_t)rn * a.Cn + cn) * rplane + (size_t)ry * a.m.W + rx;
+                    if (ok) src = ((size_t)rn * a.Cn + cn) * rplane + (size_t)ry * a.m.W + rx;
                 }
-                cp_async4_zfill(dst + i, src, ok);
+                cp_async4_zfill(dst + i, in + src, ok);
+                if (masked) cp_async4_zfill(s_mask + img * IMG_FLOATS + i, a.mask + src, ok);
             }
         }
         cp_async_commit_wait_all();
         __syncthreads();
+    }
+
+    if (MODE == 2) {
+        // ---- ReLU backward fused into the load: the error is zero where the activation output was --
+        if (masked) {
+            float4* e4 = reinterpret_cast<float4*>(s_in);
+            const float4* m4 = reinterpret_cast<const float4*>(s_mask);
+            for (int i = tid; i < 2 * IMG_FLOATS / 4; i += PT_THREADS) {
+                float4 e = e4[i];
+                const float4 mk = m4[i];
+                e.x = mk.x > 0.f ? e.x : 0.f; e.y = mk.y > 0.f ? e.y : 0.f;
+                e.z = mk.z > 0.f ? e.z : 0.f; e.w = mk.w > 0.f ? e.w : 0.f;
+                e4[i] = e;
+            }
+            __syncthreads();
+        }
+        // ---- the un-blurred tile in the gradient kernel's layout (what error_relayout_kernel writes) -
+        if (a.sgp != nullptr) {
+            const bool edges = a.edge_row || a.edge_col;
+            for (int t = tid; t < TH * 16; t += PT_THREADS) {
+                const int y = t >> 4, g = t & 15;
+                const int gy = y0 + y, j = (x0 >> 1) + 2 * g;           // float2-column of pixel x0 + 4g
+                if (gy >= H || j >= a.sgp_qp) continue;
+                float4 v0 = *reinterpret_cast<const float4*>(s_in + (y + C) * SW + PADX + 4 * g);
+                float4 v1 = *reinterpret_cast<const float4*>(s_in + IMG_FLOATS + (y + C) * SW + PADX + 4 * g);
+                if (edges) {
+                    float* p0 = &v0.x; float* p1 = &v1.x;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        int rn, ry, rx;
+                        mosaic_to_real(a.m, 2 * np, gy, x0 + 4 * g + i, &rn, &ry, &rx);   // (ry, rx) do not depend on the image
+                        if ((a.edge_row && ry == a.m.H - 1) || (a.edge_col && rx == a.m.W - 1)) p0[i] = p1[i] = 0.f;
+                    }
+                }
+                float4* dst = reinterpret_cast<float4*>(a.sgp + ((size_t)pc * H + gy) * 2 * a.sgp_qp + j);
+                dst[0] = make_float4(v0.x, v1.x, v0.z, v1.z);                 // even columns
+                dst[a.sgp_qp / 2] = make_float4(v0.y, v1.y, v0.w, v1.w);     // odd columns
+            }
+        }
     }
 
     // ---- row pass: 4 pixels of both images per task, results stored as (img0, img1) pairs.  Scalar
@@ -247,20 +302,24 @@ void launch_c(const float* in, float* out, PairBlurArgs& a, int pairs_times_c, c
     using G = TileGeom<MODE, C>;
     const bool ident = a.m.kx == 1 && a.m.ky == 1;
     // TMA needs 16-byte row pitch and base; everything else goes through the element-wise path
-    const bool use_tma = ident && (a.W & 3) == 0 && (reinterpret_cast<size_t>(in) & 15) == 0;
+    const bool use_tma = ident && (a.W & 3) == 0 && (reinterpret_cast<size_t>(in) & 15) == 0 &&
+                         (reinterpret_cast<size_t>(a.mask) & 15) == 0;
+    const size_t smem = G::SMEM + (a.mask ? G::SMEM_MASK : 0);
     static bool attr_set = false;
     if (!attr_set) {
-        DAU_CUDA_CHECK(cudaFuncSetAttribute(blur_pair_kernel<MODE, C, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::SMEM));
-        DAU_CUDA_CHECK(cudaFuncSetAttribute(blur_pair_kernel<MODE, C, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::SMEM));
+        DAU_CUDA_CHECK(cudaFuncSetAttribute(blur_pair_kernel<MODE, C, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(G::SMEM + G::SMEM_MASK)));
+        DAU_CUDA_CHECK(cudaFuncSetAttribute(blur_pair_kernel<MODE, C, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(G::SMEM + G::SMEM_MASK)));
         attr_set = true;
     }
-    CUtensorMap map;
+    CUtensorMap map, mmap;
     memset(&map, 0, sizeof(map));
+    memset(&mmap, 0, sizeof(mmap));
     if (use_tma) {
         const uint64_t dims[3] = {(uint64_t)a.W, (uint64_t)a.H, (uint64_t)a.N * a.Cn};
         const uint64_t strides[2] = {(uint64_t)a.W * 4, (uint64_t)a.H * a.W * 4};
         const uint32_t box[3] = {(uint32_t)G::SW, (uint32_t)G::ROWS, 1};
         map = make_map_f32(in, 3, dims, strides, box);
+        if (a.mask) mmap = make_map_f32(a.mask, 3, dims, strides, box);
     }
     const int gx = MODE == 3 ? a.tiles_x : (a.W + PT_W - 1) / PT_W;
     const int gy = MODE == 3 ? (a.tiles_y * 4 + G::TH - 1) / G::TH : (a.H + G::TH - 1) / G::TH;
@@ -268,8 +327,8 @@ void launch_c(const float* in, float* out, PairBlurArgs& a, int pairs_times_c, c
         const int nz = pairs_times_c - z0 < 65535 ? pairs_times_c - z0 : 65535;
         a.z0 = z0;
         const dim3 grid(gx, gy, nz);
-        if (use_tma) blur_pair_kernel<MODE, C, true><<<grid, PT_THREADS, G::SMEM, stream>>>(map, in, out, a);
-        else blur_pair_kernel<MODE, C, false><<<grid, PT_THREADS, G::SMEM, stream>>>(map, in, out, a);
+        if (use_tma) blur_pair_kernel<MODE, C, true><<<grid, PT_THREADS, smem, stream>>>(map, mmap, in, out, a);
+        else blur_pair_kernel<MODE, C, false><<<grid, PT_THREADS, smem, stream>>>(map, mmap, in, out, a);
     }
     DAU_CUDA_CHECK(cudaGetLastError());
 }
@@ -296,7 +355,7 @@ void fill_pairs(float2* dst, const float* f, int kb) {
 }  // namespace
 
 void launch_blur_single_paired(const float* in, float* out_paired, const Mosaic& m, int Cn, int kb,
-                               const float* fx, const float* fy, cudaStream_t stream) {
+                               const float* fx, const float* fy, cudaStream_t stream, const ErrorSideArgs* extra) {
     const int N = m.Nv, H = m.Hv, W = m.Wv;
     DAU_CHECK(m.gap >= (kb >> 1) || (m.kx == 1 && m.ky == 1), 4,
               "blur wider than the mosaic gap: call dau_set_sigma_hint before dau_reshape");
@@ -306,6 +365,11 @@ void launch_blur_single_paired(const float* in, float* out_paired, const Mosaic&
     fill_pairs(a.fy[0], fy, kb);
     a.H = H; a.W = W; a.N = N; a.Cn = Cn; a.m = m;
     a.qv = (W + 3) / 4; a.qp = (a.qv + 1) / 2 * 2;
+    if (extra) {
+        a.mask = extra->mask; a.sgp = reinterpret_cast<float2*>(extra->sgp);
+        a.sgp_qp = ((W + 1) / 2 + 1) / 2 * 2;
+        a.edge_row = extra->edge_row; a.edge_col = extra->edge_col;
+    }
     launch_pair<2>(in, out_paired, a, kb, ((N + 1) / 2) * Cn, stream);
 }
 

@@ -127,6 +127,22 @@ dau_status_t dau_backward(dau_handle_t* h, const float* bottom, const float* top
     });
 }
 
+dau_status_t dau_set_activation(dau_handle_t* h, int activation) {
+    if (!h) return fail(DAU_ERR_INVALID_ARGUMENT, "dau_set_activation: NULL handle");
+    return guarded([&] { h->layer->set_activation(activation); });
+}
+
+dau_status_t dau_backward_act(dau_handle_t* h, const float* bottom, const float* top_data, const float* top_error,
+                              const float* w, const float* mu1, const float* mu2, const float* sigma,
+                              float* bottom_error, float* dw, float* dmu1, float* dmu2, float* dsigma,
+                              float* dbias, unsigned flags, void* ws, size_t ws_bytes, void* stream) {
+    if (!h) return fail(DAU_ERR_INVALID_ARGUMENT, "dau_backward_act: NULL handle");
+    return guarded([&] {
+        h->layer->Backward_gpu(bottom, top_error, w, mu1, mu2, sigma, bottom_error, dw, dmu1, dmu2,
+                               dsigma, dbias, flags, ws, ws_bytes, (cudaStream_t)stream, top_data);
+    });
+}
+
 dau_status_t dau_get_kernels(const dau_settings_t* settings, float sigma, int* kb_out, float* out6,
                              size_t cap) {
     if (!settings || !kb_out || !out6) return fail(DAU_ERR_INVALID_ARGUMENT, "dau_get_kernels: NULL argument");

@@ -65,6 +65,7 @@ struct TGatherParams {
     int tiles_x, nstage;
     int stage_bytes;       // tile + records, multiple of 128
     int debug;
+    int relu;              // epilogue: store max(0, y + bias)  
     Mosaic m;              // N, H, W above are the mosaic extents; `out` is the real NCHW tensor
 };
 
@@ -188,7 +189,10 @@ dau_gather_tma_kernel(const __grid_constant__ CUtensorMap in_map, const TGatherP
             if (y >= H) continue;
             float v[C];
 #pragma unroll
-            for (int c = 0; c < C; ++c) v[c] = (img == 0 ? acc[r][c].x : acc[r][c].y) + bv;
+            for (int c = 0; c < C; ++c) {
+                v[c] = (img == 0 ? acc[r][c].x : acc[r][c].y) + bv;
+                if (p.relu) v[c] = fmaxf(v[c], 0.f);
+            }
             if (ident) {
                 float* orow = p.out + ((size_t)n * p.Cout + co) * rplane + (size_t)y * W;
                 if (vec) {
@@ -270,7 +274,7 @@ bool plan_gather_tma(int N, int Cin, int Cout, int G, int H, int W, int max_off,
 }
 
 void launch_gather_tma(const GatherPlan& plan, const float* in_paired, const UnitRec* table, const float* bias,
-                       float* out, const Mosaic& m, int Cin, int Cout, int G, cudaStream_t stream) {
+                       float* out, const Mosaic& m, int Cin, int Cout, int G, cudaStream_t stream, int relu) {
     const int N = m.Nv, H = m.Hv, W = m.Wv;
     // tensor map of the paired gather layout: dims (q*2+i, p, y, plane)
     const uint64_t qv = (W + 3) / 4, qp = (qv + 1) / 2 * 2;
@@ -284,7 +288,7 @@ void launch_gather_tma(const GatherPlan& plan, const float* in_paired, const Uni
     p.N = N; p.Cin = Cin; p.Cout = Cout; p.G = G; p.H = H; p.W = W;
     p.tiles_x = (W + TW - 1) / TW; p.nstage = plan.nstage;
     p.stage_bytes = plan.stage_words * 4;
-    p.m = m;
+    p.m = m; p.relu = relu;
     p.debug = getenv("DAU_DEBUG") ? atoi(getenv("DAU_DEBUG")) : 0;
     switch (plan.variant) {
         case 0: launch_t<4>(plan, map, p, stream); break;

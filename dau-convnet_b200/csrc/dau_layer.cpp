@@ -150,6 +150,11 @@ const BlurFactors& DAUConvLayerB200::factors_for(const float* sigma_dev, cudaStr
     return factors_;
 }
 
+void DAUConvLayerB200::set_activation(int act) {
+    DAU_CHECK(act == DAU_ACT_NONE || act == DAU_ACT_RELU, 1, "activation must be DAU_ACT_NONE or DAU_ACT_RELU");
+    activation_ = act;
+}
+
 void DAUConvLayerB200::enable_timing(bool e) {
     timing_ = e;
     if (e && slots_[0].empty()) {
@@ -229,7 +234,8 @@ void DAUConvLayerB200::Forward_gpu(const float* bottom, float* w, float* mu1, fl
     toc(0, 2, stream);
 
     tic(0, 3, stream);
-    launch_gather_tma(fwd_plan_, xb, table, st_.bias_term ? bias : nullptr, top, mosaic_, S_, F_, G_, stream);
+    launch_gather_tma(fwd_plan_, xb, table, st_.bias_term ? bias : nullptr, top, mosaic_, S_, F_, G_, stream,
+                      activation_ == DAU_ACT_RELU ? 1 : 0);
     toc(0, 3, stream);
 }
 
@@ -237,9 +243,13 @@ void DAUConvLayerB200::Backward_gpu(const float* bottom, const float* top_error,
                                     const float* mu1, const float* mu2, const float* sigma,
                                     float* bottom_error, float* dw, float* dmu1, float* dmu2,
                                     float* dsigma, float* dbias, unsigned flags, void* ws,
-                                    size_t ws_bytes, cudaStream_t stream) {
+                                    size_t ws_bytes, cudaStream_t stream, const float* top_data) {
     DAU_CHECK(shaped_, 3, "Backward_gpu called before Reshape");
     DAU_CHECK(bottom && top_error && w && mu1 && mu2, 1, "NULL tensor pointer");
+    DAU_CHECK(activation_ == DAU_ACT_NONE || top_data, 1,
+              "an activation is fused into this layer: the backward pass needs top_data (dau_backward_act)");
+    // ReLU backward fused into every load of the top error (row f3): error := 0 where top_data <= 0
+    const float* act = activation_ == DAU_ACT_RELU ? top_data : nullptr;
     DAU_CHECK(ws != nullptr && ws_bytes >= bwd_ws_, 3, "backward workspace missing or too small");
     DAU_CUDA_CHECK(cudaSetDevice(device_));
     if (timing_) for (auto& sl : slots_[1]) sl.used = false;
@@ -275,11 +285,21 @@ void DAUConvLayerB200::Backward_gpu(const float* bottom, const float* top_error,
         launch_unit_prep(ua, nullptr, want_input ? btable : nullptr, want_params ? gtable : nullptr, flag, stream);
         toc(1, 1, stream);
     }
+    const int mrow = st_.ignore_edge_gradients && edge_rule(H_) ? 1 : 0;
+    const int mcol = st_.ignore_edge_gradients && edge_rule(W_) ? 1 : 0;
+    if (want_input) {
+        // blur the error with the rotated filter (base_dau_conv_layer.cu:278-288); the same kernel
+        // hands the un-blurred tile to the gradient kernel in its own layout, so the error is read
+        // from HBM once
+        tic(1, 4, stream);
+        ErrorSideArgs ex;
+        ex.mask = act; ex.sgp = want_params ? esg : nullptr; ex.edge_row = mrow; ex.edge_col = mcol;
+        launch_blur_single_paired(top_error, eb, mosaic_, F_, f.kb, f.err_x, f.err_y, stream, &ex);
+        toc(1, 4, stream);
+    }
     if (want_params) {
         tic(1, 2, stream);
-        const int mrow = st_.ignore_edge_gradients && edge_rule(H_) ? 1 : 0;
-        const int mcol = st_.ignore_edge_gradients && edge_rule(W_) ? 1 : 0;
-        launch_error_relayout(top_error, esg, mosaic_, F_, mrow, mcol, stream);
+        if (!want_input) launch_error_relayout(top_error, esg, mosaic_, F_, mrow, mcol, stream, act);
         launch_grad_tma(grad_plan_, xk, esg, gtable, partial, mosaic_.Nv, S_, F_, G_, mosaic_.Hv, mosaic_.Wv, stream);
         toc(1, 2, stream);
         tic(1, 3, stream);
@@ -295,18 +315,14 @@ void DAUConvLayerB200::Backward_gpu(const float* bottom, const float* top_error,
         toc(1, 3, stream);
     }
     if (want_input) {
-        // blur the error with the rotated filter, then gather with -mu and the parameters read
-        // transposed (base_dau_conv_layer.cu:278-325)
-        tic(1, 4, stream);
-        launch_blur_single_paired(top_error, eb, mosaic_, F_, f.kb, f.err_x, f.err_y, stream);
-        toc(1, 4, stream);
+        // gather with -mu and the parameters read transposed (base_dau_conv_layer.cu:290-325)
         tic(1, 5, stream);
         launch_gather_tma(bwd_plan_, eb, btable, nullptr, bottom_error, mosaic_, F_, S_, G_, stream);
         toc(1, 5, stream);
     }
     if ((flags & DAU_GRAD_BIAS) && st_.bias_term && dbias) {
         tic(1, 6, stream);
-        launch_bias_grad(top_error, dbias, N_, F_, H_ * W_, stream);
+        launch_bias_grad(top_error, act, dbias, N_, F_, H_ * W_, stream);
         toc(1, 6, stream);
     }
 }

@@ -31,7 +31,14 @@ public:
     void Backward_gpu(const float* bottom, const float* top_error, const float* w, const float* mu1,
                       const float* mu2, const float* sigma, float* bottom_error, float* dw,
                       float* dmu1, float* dmu2, float* dsigma, float* dbias, unsigned flags,
-                      void* ws, size_t ws_bytes, cudaStream_t stream);
+                      void* ws, size_t ws_bytes, cudaStream_t stream, const float* top_data = nullptr);
+
+    // Fused epilogue / prologue (the activation the Python layer applies
+    // right after the op, dau_conv.py:500-526): with DAU_ACT_RELU Forward_gpu stores
+    // max(0, y + bias) and Backward_gpu, given the forward output as top_data, takes the top error
+    // as zero wherever that output was not positive.
+    void set_activation(int act);
+    int activation() const { return activation_; }
 
     // sigma known to the caller: skips the blocking device read of sigma[0] in every call (the
     // reference reads it once in LayerSetUp, base_dau_conv_layer.hpp:266-275).  Reshape sizes the
@@ -67,6 +74,7 @@ private:
     size_t off_fwd_blur_ = 0, off_fwd_table_ = 0, off_fwd_flag_ = 0;
     size_t off_bwd_xk_ = 0, off_bwd_esg_ = 0, off_bwd_eb_ = 0, off_bwd_table_ = 0, off_bwd_gtable_ = 0,
            off_bwd_partial_ = 0, off_bwd_flag_ = 0;
+    int activation_ = 0;
     float sigma_hint_ = 0.f;
     float cached_sigma_ = -1.f;
     BlurFactors factors_{};

@@ -10,7 +10,8 @@ namespace {
 // (2j, 2j+1) of one row of both mosaic images of the pair; the float2 stores are coalesced.
 __global__ void __launch_bounds__(256) error_relayout_kernel(const float* __restrict__ err, float2* __restrict__ out,
                                                              const __grid_constant__ Mosaic m, int F, int qp,
-                                                             int mask_row, int mask_col) {
+                                                             int mask_row, int mask_col,
+                                                             const float* __restrict__ act) {
     const int pf = blockIdx.x;                            // (pair, feature)
     const int np = pf / F, f = pf - np * F;
     const int idx = blockIdx.y * 256 + threadIdx.x;       // (row, column pair) of the mosaic plane
@@ -27,7 +28,12 @@ __global__ void __launch_bounds__(256) error_relayout_kernel(const float* __rest
             for (int img = 0; img < 2; ++img) {
                 const int n = 2 * np + img;
                 if (n >= m.N) continue;
-                const float2 t = __ldg(reinterpret_cast<const float2*>(err + ((size_t)n * F + f) * rplane + (size_t)vy * m.W + x));
+                const size_t at = ((size_t)n * F + f) * rplane + (size_t)vy * m.W + x;
+                float2 t = __ldg(reinterpret_cast<const float2*>(err + at));
+                if (act) {                                // ReLU backward: zero where the activation output was
+                    const float2 a2 = __ldg(reinterpret_cast<const float2*>(act + at));
+                    t.x = a2.x > 0.f ? t.x : 0.f; t.y = a2.y > 0.f ? t.y : 0.f;
+                }
                 v[0][img] = t.x;
                 v[1][img] = (mask_col && x + 1 == m.W - 1) ? 0.f : t.y;
             }
@@ -41,7 +47,8 @@ __global__ void __launch_bounds__(256) error_relayout_kernel(const float* __rest
                 int rn, ry, rx;
                 if (vx < m.Wv && nv < m.Nv && mosaic_to_real(m, nv, vy, vx, &rn, &ry, &rx)) {
                     const bool dead = (mask_row && ry == m.H - 1) || (mask_col && rx == m.W - 1);
-                    if (!dead) v[c][img] = __ldg(err + ((size_t)rn * F + f) * rplane + (size_t)ry * m.W + rx);
+                    const size_t at = ((size_t)rn * F + f) * rplane + (size_t)ry * m.W + rx;
+                    if (!dead && !(act && !(__ldg(act + at) > 0.f))) v[c][img] = __ldg(err + at);
                 }
             }
     }
@@ -51,13 +58,13 @@ __global__ void __launch_bounds__(256) error_relayout_kernel(const float* __rest
 }  // namespace
 
 void launch_error_relayout(const float* err, float* out_sg, const Mosaic& m, int F, int mask_row, int mask_col,
-                           cudaStream_t stream) {
+                           cudaStream_t stream, const float* act_mask) {
     const int qv = (m.Wv + 1) / 2, qp = (qv + 1) / 2 * 2;
     const long long total = (long long)((m.Nv + 1) / 2) * F;
     const int blocks_y = (m.Hv * qp + 255) / 256;
     DAU_CHECK(total < (1LL << 31) && blocks_y <= 65535, 4, "shape too large for the error re-layout grid");
     error_relayout_kernel<<<dim3((unsigned)total, blocks_y), 256, 0, stream>>>(err, reinterpret_cast<float2*>(out_sg), m, F, qp,
-                                                                           mask_row, mask_col);
+                                                                           mask_row, mask_col, act_mask);
     DAU_CUDA_CHECK(cudaGetLastError());
 }
 

@@ -96,14 +96,19 @@ __global__ void grad_finalize_kernel(GradFinalizeArgs a) {
 }
 
 // dbias[f] += sum_{n,hw} err[n,f,hw]   (reference: cublasSgemv with a ones vector,
-// base_dau_conv_layer.cpp:1116-1126).  One CTA per feature.
-__global__ void __launch_bounds__(256) bias_grad_kernel(const float* __restrict__ err, float* dbias,
-                                                       int N, int F, int HW) {
+// base_dau_conv_layer.cpp:1116-1126).  grid = (F, image slices); with `act` the error counts only
+// where the activation output was positive (ReLU backward fused into the load).
+__global__ void __launch_bounds__(256) bias_grad_kernel(const float* __restrict__ err, const float* __restrict__ act,
+                                                       float* dbias, int N, int F, int HW) {
     const int f = blockIdx.x;
     float acc = 0.f;
-    for (int n = 0; n < N; ++n) {
-        const float* p = err + ((size_t)n * F + f) * HW;
-        for (int i = threadIdx.x; i < HW; i += 256) acc += p[i];
+    for (int n = blockIdx.y; n < N; n += gridDim.y) {
+        const size_t base = ((size_t)n * F + f) * HW;
+        if (act) {
+            for (int i = threadIdx.x; i < HW; i += 256) acc += act[base + i] > 0.f ? err[base + i] : 0.f;
+        } else {
+            for (int i = threadIdx.x; i < HW; i += 256) acc += err[base + i];
+        }
     }
     __shared__ float red[8];
     for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
@@ -112,7 +117,7 @@ __global__ void __launch_bounds__(256) bias_grad_kernel(const float* __restrict_
     if (threadIdx.x == 0) {
         float t = 0.f;
         for (int i = 0; i < 8; ++i) t += red[i];
-        dbias[f] += t;
+        atomicAdd(dbias + f, t);
     }
 }
 
@@ -156,8 +161,9 @@ void launch_grad_finalize(const GradFinalizeArgs& a, cudaStream_t stream) {
     DAU_CUDA_CHECK(cudaGetLastError());
 }
 
-void launch_bias_grad(const float* err, float* dbias, int N, int F, int HW, cudaStream_t stream) {
-    bias_grad_kernel<<<F, 256, 0, stream>>>(err, dbias, N, F, HW);
+void launch_bias_grad(const float* err, const float* act, float* dbias, int N, int F, int HW, cudaStream_t stream) {
+    const int slices = N < 16 ? N : 16;
+    bias_grad_kernel<<<dim3(F, slices), 256, 0, stream>>>(err, act, dbias, N, F, HW);
     DAU_CUDA_CHECK(cudaGetLastError());
 }
 

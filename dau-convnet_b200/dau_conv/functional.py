@@ -23,10 +23,14 @@ OP_ATTRS = dict(
     merge_threshold=1, unit_testing=False, mu_learning_rate_factor=1.0, single_dim_kernel=False,
     forbid_positive_dim1=False, use_interpolation=True,
 )
+# beyond the TF op: settings of BaseDAUConvLayer the fused layer path uses (DAUConvSettings.bias_term,
+# base_dau_conv_layer.hpp:112)
+EXT_ATTRS = dict(bias_term=False)
 
 
 def _settings_from_attrs(attrs):
     a = dict(OP_ATTRS)
+    a.update(EXT_ATTRS)
     for k, v in attrs.items():
         if k not in a:
             raise TypeError("DAUConv: unknown attribute %r" % k)
@@ -45,6 +49,7 @@ def _settings_from_attrs(attrs):
         single_dimension_kernel=int(bool(a["single_dim_kernel"])),
         forbid_positive_dim1=int(bool(a["forbid_positive_dim1"])),
         use_interpolation=int(bool(a["use_interpolation"])),
+        bias_term=int(bool(a["bias_term"])),
         unit_bounds_guard=0,           # the TF op disables the guard (dau_conv_op.cpp:283)
         learn_sigma=1,                 # enable_sigma_learning(true) (dau_conv_grad_op.cpp:272)
     )
@@ -109,9 +114,14 @@ class DAULayerHandle(object):
         return int(_lib.lib.dau_launch_count(self._h))
 
     # -- the two calls of the contract ---------------------------------------------------------
-    def forward(self, x, w, mu1, mu2, sigma, bias=None, out=None):
+    def set_activation(self, activation):
+        """dau_set_activation: DAU_ACT_NONE (0) or DAU_ACT_RELU (1), fused into forward / backward."""
+        _lib.check(_lib.lib.dau_set_activation(self._h, int(activation)))
+
+    def forward(self, x, w, mu1, mu2, sigma, bias=None, out=None, activation=_lib.ACT_NONE):
         N, S, H, W = x.shape
         self.reshape(N, S, H, W)
+        self.set_activation(activation)
         F = self.settings.num_output
         if out is None:
             out = torch.empty((N, F, H, W), dtype=torch.float32, device=x.device)
@@ -123,20 +133,27 @@ class DAULayerHandle(object):
             ws.data_ptr(), ws.numel(), stream))
         return out
 
-    def backward(self, x, top_error, w, mu1, mu2, sigma, flags=_lib.GRAD_ALL, grads=None, dbias=None):
-        """Returns (dx, dw, dmu1, dmu2, dsigma); param grads are accumulated into `grads` if given."""
+    def backward(self, x, top_error, w, mu1, mu2, sigma, flags=_lib.GRAD_ALL, grads=None, dbias=None,
+                 top_data=None, activation=_lib.ACT_NONE):
+        """Returns (dx, dw, dmu1, dmu2, dsigma); param grads are accumulated into `grads` if given.
+        With a fused activation, `top_data` is the forward output and `top_error` the gradient
+        w.r.t. that (activated) output: dau_backward_act."""
         N, S, H, W = x.shape
         self.reshape(N, S, H, W)
+        self.set_activation(activation)
         dx = torch.empty_like(x) if flags & _lib.GRAD_INPUT else None
         if grads is None:
             grads = [torch.zeros_like(w) for _ in range(4)]     # the TF op pre-zeroes (grad_op.cpp:202-205)
         ws = self.workspace(self.bwd_bytes)
         stream = torch.cuda.current_stream(x.device).cuda_stream
-        _lib.check(_lib.lib.dau_backward(
-            self._h, x.data_ptr(), top_error.data_ptr(), w.data_ptr(), mu1.data_ptr(), mu2.data_ptr(),
-            sigma.data_ptr(), dx.data_ptr() if dx is not None else None,
-            grads[0].data_ptr(), grads[1].data_ptr(), grads[2].data_ptr(), grads[3].data_ptr(),
-            dbias.data_ptr() if dbias is not None else None, flags, ws.data_ptr(), ws.numel(), stream))
+        tail = (w.data_ptr(), mu1.data_ptr(), mu2.data_ptr(),
+                sigma.data_ptr(), dx.data_ptr() if dx is not None else None,
+                grads[0].data_ptr(), grads[1].data_ptr(), grads[2].data_ptr(), grads[3].data_ptr(),
+                dbias.data_ptr() if dbias is not None else None, flags, ws.data_ptr(), ws.numel(), stream)
+        if activation != _lib.ACT_NONE:
+            _lib.check(_lib.lib.dau_backward_act(self._h, x.data_ptr(), top_data.data_ptr(), top_error.data_ptr(), *tail))
+        else:
+            _lib.check(_lib.lib.dau_backward(self._h, x.data_ptr(), top_error.data_ptr(), *tail))
         return (dx,) + tuple(grads)
 
 
@@ -243,3 +260,53 @@ class _DAUConvFunction(torch.autograd.Function):
 def dau_conv(input, weights, mu1, mu2, sigma, sigma_value=None, **attrs):
     """Differentiable DAUConv (forward + registered gradient)."""
     return _DAUConvFunction.apply(input, weights, mu1, mu2, sigma, attrs, sigma_value)
+
+
+class _DAUConvFusedFunction(torch.autograd.Function):
+    """DAUConv followed by the bias add and activation of the Python layer (dau_conv.py:500-526),
+    both fused into the operator's kernels: the epilogue of the forward gather stores
+    act(y + bias), the backward pass masks the incoming gradient as it loads it."""
+
+    @staticmethod
+    def forward(ctx, input, weights, mu1, mu2, sigma, bias, attrs, sigma_value, activation):
+        ctx.attrs, ctx.activation = attrs, activation
+        ctx.sigma_value = _sigma_of(sigma, sigma_value)
+        _check_inputs(input, weights, mu1, mu2, sigma, attrs)
+        h = get_handle(input.device, **attrs)
+        h.set_sigma_hint(ctx.sigma_value)
+        out = h.forward(input.contiguous(), weights.contiguous(), mu1.contiguous(), mu2.contiguous(),
+                        sigma.contiguous(), bias=bias.contiguous() if bias is not None else None,
+                        activation=activation)
+        ctx.save_for_backward(input, weights, mu1, mu2, sigma, out)
+        return out
+
+    @staticmethod
+    def backward(ctx, grad):
+        input, weights, mu1, mu2, sigma, out = ctx.saved_tensors
+        need = ctx.needs_input_grad
+        flags = 0
+        if need[0]:
+            flags |= _lib.GRAD_INPUT
+        if any(need[1:5]):
+            flags |= _lib.GRAD_W | _lib.GRAD_MU1 | _lib.GRAD_MU2 | _lib.GRAD_SIGMA
+        dbias = None
+        if need[5]:
+            flags |= _lib.GRAD_BIAS
+            dbias = torch.zeros(weights.shape[-1], dtype=torch.float32, device=grad.device)
+        h = get_handle(input.device, **ctx.attrs)
+        h.set_sigma_hint(ctx.sigma_value)
+        dx, dw, dm1, dm2, dsg = h.backward(input.contiguous(), grad.contiguous(), weights.contiguous(),
+                                           mu1.contiguous(), mu2.contiguous(), sigma.contiguous(), flags=flags,
+                                           dbias=dbias, top_data=out, activation=ctx.activation)
+        return (dx if need[0] else None, dw if need[1] else None, dm1 if need[2] else None,
+                dm2 if need[3] else None, dsg if need[4] else None, dbias, None, None, None)
+
+
+def dau_conv_fused(input, weights, mu1, mu2, sigma, bias=None, activation=None, sigma_value=None, **attrs):
+    """Differentiable act(DAUConv(input) + bias) in ONE pass of the operator (SURVEY section 8
+    row f3).  activation: None or "relu"."""
+    if activation not in (None, "relu"):
+        raise ValueError("dau_conv_fused: activation must be None or 'relu'")
+    attrs = dict(attrs, bias_term=bias is not None)
+    act = _lib.ACT_RELU if activation == "relu" else _lib.ACT_NONE
+    return _DAUConvFusedFunction.apply(input, weights, mu1, mu2, sigma, bias, attrs, sigma_value, act)

@@ -174,13 +174,15 @@ class DAUConv2d(nn.Module):
         sigma = self.sigma.reshape(1, 1, 1, 1).expand(self.weights.shape)      # tiled view (:418-430)
         if self.dau_sigma_trainable or self._sigma_value is None:
             self._sigma_value = float(self.sigma.detach().reshape(-1)[0])      # one blocking read
-        out = Fn.dau_conv(inputs, self.weights, mu1, mu2, sigma, sigma_value=self._sigma_value,
-                          **self._op_attrs())
+        # bias add and ReLU (:500-526) are element-wise, so they commute with the stride slicing and
+        # run inside the operator's own kernels; any other activation is applied afterwards
+        relu = self.activation in (torch.relu, nn.functional.relu) or isinstance(self.activation, nn.ReLU)
+        out = Fn.dau_conv_fused(inputs, self.weights, mu1, mu2, sigma, bias=self.bias if self.use_bias else None,
+                                activation="relu" if relu else None, sigma_value=self._sigma_value,
+                                **self._op_attrs())
         if self.strides > 1:                                  # emulated by slicing (:496-498)
             out = out[:, :, ::self.strides, ::self.strides]
-        if self.use_bias:
-            out = out + self.bias.reshape(1, -1, 1, 1)
-        return self.activation(out) if self.activation is not None else out
+        return self.activation(out) if (self.activation is not None and not relu) else out
 
 
 class DAUConv1d(DAUConv2d):

@@ -113,6 +113,23 @@ dau_status_t dau_backward(dau_handle_t* h, const float* bottom_dev, const float*
                           float* dbias_dev, unsigned flags,
                           void* workspace_dev, size_t workspace_bytes, void* stream);
 
+/* Fused epilogue / prologue (the steps the reference's Python layer runs right after the op:
+ * bias add and activation, plugins/tensorflow/dau_conv/dau_conv.py:500-526; ReLU is what every
+ * reference model uses).  With DAU_ACT_RELU dau_forward stores max(0, y + bias) and
+ * dau_backward_act -- dau_backward plus the forward OUTPUT top_data[N,F,H,W] -- takes the top
+ * error as zero wherever top_data <= 0 while it loads it (blur, gradient and bias-gradient
+ * kernels alike), so neither the activation nor its backward mask cost a pass over HBM.
+ * With DAU_ACT_NONE dau_backward_act ignores top_data and equals dau_backward. */
+enum { DAU_ACT_NONE = 0, DAU_ACT_RELU = 1 };
+dau_status_t dau_set_activation(dau_handle_t* h, int activation);
+dau_status_t dau_backward_act(dau_handle_t* h, const float* bottom_dev, const float* top_data_dev,
+                              const float* top_error_dev,
+                              const float* w_dev, const float* mu1_dev, const float* mu2_dev,
+                              const float* sigma_dev, float* bottom_error_dev,
+                              float* dw_dev, float* dmu1_dev, float* dmu2_dev, float* dsigma_dev,
+                              float* dbias_dev, unsigned flags,
+                              void* workspace_dev, size_t workspace_bytes, void* stream);
+
 /* DAUKernelCompute for one unit (w=1, mu=0): six Kb x Kb HOST arrays, row-major, axis 0 = y.
  * Order: blur, d_w, d_mu1, d_mu2, d_sigma, d_error.  *kb_out = 2*ceil(5*sigma)+1. */
 dau_status_t dau_get_kernels(const dau_settings_t* settings, float sigma, int* kb_out,

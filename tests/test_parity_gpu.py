@@ -260,3 +260,84 @@ def test_full_size_properties(cfg):
     ref = G * torch.nn.functional.conv2d(x.sum(1, keepdim=True), k, padding=3)
     assert float((y1[:, :1] - ref).abs().max()) <= 1e-4 * float(ref.abs().max())
     assert float((y1 - y1[:, :1]).abs().max()) == 0.0     # every feature saw the same units
+
+
+# ---- row f3: bias + ReLU fused into the forward store, ReLU mask fused into every error load ------
+FUSED_SHAPES = [
+    (4, 64, 64, 8, 16, (1, 2), 9, 3),      # identity mosaic, TMA blur path
+    (3, 64, 40, 4, 6, (2, 2), 9, 3),       # odd batch (second image of the last pair is not there)
+    (2, 30, 21, 5, 7, (1, 3), 9, 3.9),     # odd width: element-wise staging
+    (9, 13, 13, 3, 5, (1, 2), 9, 3.9),     # mosaic
+    (5, 27, 27, 8, 16, (1, 2), 17, 6),     # mosaic, larger kernel
+]
+
+
+@pytest.mark.parametrize("shape", FUSED_SHAPES, ids=["x".join(str(v) for v in s[:5]) for s in FUSED_SHAPES])
+@pytest.mark.parametrize("which", ["all", "input_only", "params_only"])
+@pytest.mark.parametrize("edge", [False, True], ids=["exact", "edgemask"])
+def test_fused_bias_relu_matches_unfused(shape, which, edge):
+    """act(DAUConv(x) + b) and its gradients through dau_conv_fused (one pass of the operator) against
+    the un-fused composition dau_conv -> torch add -> torch relu, whose DAU part is oracle-checked
+    above.  Forward is the same arithmetic followed by max(0, .): compared tightly."""
+    import torch
+    import dau_conv
+    x, err, w, mu1, mu2, ks = _case(shape, 77)
+    N, W, H, S, F, units, _, _ = shape
+    dev = torch.device("cuda:0")
+    rng = np.random.default_rng(5)
+    b = (0.2 * rng.standard_normal(F)).astype(np.float32)
+    sig = np.full(w.shape, 0.5, np.float32)
+    attrs = dict(num_output=F, number_units_x=units[0], number_units_y=units[1], kernel_size=ks, pad=(ks - 1) // 2,
+                 unit_testing=edge)
+
+    def leaves():
+        t = [torch.from_numpy(a.copy()).to(dev) for a in (x, w, mu1, mu2, sig, b)]
+        t[0].requires_grad_(which != "params_only")
+        for v in t[1:]:
+            v.requires_grad_(which != "input_only")
+        return t
+
+    e = torch.from_numpy(err).to(dev)
+    ref = leaves()
+    y_ref = torch.relu(dau_conv.dau_conv(*ref[:5], sigma_value=0.5, **attrs) + ref[5].reshape(1, -1, 1, 1))
+    y_ref.backward(e)
+    got = leaves()
+    y = dau_conv.dau_conv_fused(*got[:5], bias=got[5], activation="relu", sigma_value=0.5, **attrs)
+    y.backward(e)
+    torch.cuda.synchronize()
+    assert float((y.detach() < 0).sum()) == 0
+    assert 0.05 < float((y.detach() == 0).float().mean()) < 0.95        # the mask really cuts
+    close(y.detach().cpu().numpy(), y_ref.detach().cpu().numpy(), "relu(y + b)")
+    names = ["dx", "dw", "dmu1", "dmu2", "dsigma", "dbias"]
+    for name, g, r in zip(names, got, ref):
+        if r.grad is None:
+            assert g.grad is None, name
+            continue
+        close(g.grad.cpu().numpy(), r.grad.cpu().numpy(), name, scale_atol=name != "dx")
+
+
+def test_fused_activation_needs_top_data_and_none_equals_plain_backward():
+    import torch
+    import dau_conv
+    from dau_conv import _lib
+    x, err, w, mu1, mu2, ks = _case((2, 32, 32, 4, 4, (1, 2), 9, 3), 3)
+    dev = torch.device("cuda:0")
+    sig = np.full(w.shape, 0.5, np.float32)
+    t = [torch.from_numpy(a).to(dev) for a in (x, w, mu1, mu2, sig)]
+    e = torch.from_numpy(err).to(dev)
+    h = dau_conv.get_handle(dev, num_output=4, number_units_x=1, number_units_y=2, kernel_size=ks, pad=4)
+    h.set_sigma_hint(0.5)
+    y = h.forward(*t)
+    plain = h.backward(t[0], e, *t[1:])
+    same = h.backward(t[0], e, *t[1:], top_data=y, activation=_lib.ACT_NONE)
+    for a, b_ in zip(plain, same):
+        assert torch.equal(a, b_)
+    h.set_activation(_lib.ACT_RELU)
+    ws = h.workspace(h.bwd_bytes)
+    rc = _lib.lib.dau_backward(h._h, t[0].data_ptr(), e.data_ptr(), *[v.data_ptr() for v in t[1:]],
+                               plain[0].data_ptr(), *[g.data_ptr() for g in plain[1:]], None, _lib.GRAD_ALL,
+                               ws.data_ptr(), ws.numel(), None)
+    assert rc != 0 and "top_data" in _lib.lib.dau_last_error().decode()
+    with pytest.raises(dau_conv.DAUError):
+        h.set_activation(7)
+    h.set_activation(_lib.ACT_NONE)
