@@ -62,6 +62,7 @@ struct PairBlurArgs {
     float2* sgp;                 // also emit the (masked) input as SGP[n/2][c][y][x%2][x/2][n%2] for the gradient kernel
     int sgp_qp;                  // padded float2-columns per SGP plane
     int edge_row, edge_col;      // ignore_edge_gradients: SGP gets zeros in the last real row / column
+    int crop;                    // `in` / `mask` are [.., m.H-2crop, m.W-2crop] planes centred in the full grid
 };
 
 template <int MODE, int C>
@@ -121,7 +122,8 @@ blur_pair_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
         __syncthreads();                                     // barrier initialised (and zeros visible)
         mbar_wait(bar, 0);
     } else {
-        const size_t rplane = (size_t)a.m.H * a.m.W;
+        const int crop = a.crop, RH = a.m.H - 2 * crop, RW = a.m.W - 2 * crop;
+        const size_t rplane = (size_t)RH * RW;
 #pragma unroll
         for (int img = 0; img < 2; ++img) {
             const int n = 2 * np + img;                      // mosaic image
@@ -134,7 +136,9 @@ blur_pair_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
                 if (ok) {
                     int rn = n, ry = gy, rx = gx;
                     if (!ident) ok = mosaic_to_real(a.m, n, gy, gx, &rn, &ry, &rx);
-                    if (ok) src = ((size_t)rn * a.Cn + cn) * rplane + (size_t)ry * a.m.W + rx;
+                    ry -= crop; rx -= crop;
+                    ok = ok && ry >= 0 && ry < RH && rx >= 0 && rx < RW;
+                    if (ok) src = ((size_t)rn * a.Cn + cn) * rplane + (size_t)ry * RW + rx;
                 }
                 cp_async4_zfill(dst + i, in + src, ok);
                 if (masked) cp_async4_zfill(s_mask + img * IMG_FLOATS + i, a.mask + src, ok);
@@ -173,7 +177,7 @@ blur_pair_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
                     for (int i = 0; i < 4; ++i) {
                         int rn, ry, rx;
                         mosaic_to_real(a.m, 2 * np, gy, x0 + 4 * g + i, &rn, &ry, &rx);   // (ry, rx) do not depend on the image
-                        if ((a.edge_row && ry == a.m.H - 1) || (a.edge_col && rx == a.m.W - 1)) p0[i] = p1[i] = 0.f;
+                        if ((a.edge_row && ry == a.m.H - 1 - a.crop) || (a.edge_col && rx == a.m.W - 1 - a.crop)) p0[i] = p1[i] = 0.f;
                     }
                 }
                 float4* dst = reinterpret_cast<float4*>(a.sgp + ((size_t)pc * H + gy) * 2 * a.sgp_qp + j);
@@ -302,7 +306,7 @@ void launch_c(const float* in, float* out, PairBlurArgs& a, int pairs_times_c, c
     using G = TileGeom<MODE, C>;
     const bool ident = a.m.kx == 1 && a.m.ky == 1;
     // TMA needs 16-byte row pitch and base; everything else goes through the element-wise path
-    const bool use_tma = ident && (a.W & 3) == 0 && (reinterpret_cast<size_t>(in) & 15) == 0 &&
+    const bool use_tma = ident && a.crop == 0 && (a.W & 3) == 0 && (reinterpret_cast<size_t>(in) & 15) == 0 &&
                          (reinterpret_cast<size_t>(a.mask) & 15) == 0;
     const size_t smem = G::SMEM + (a.mask ? G::SMEM_MASK : 0);
     static bool attr_set = false;
@@ -368,7 +372,7 @@ void launch_blur_single_paired(const float* in, float* out_paired, const Mosaic&
     if (extra) {
         a.mask = extra->mask; a.sgp = reinterpret_cast<float2*>(extra->sgp);
         a.sgp_qp = ((W + 1) / 2 + 1) / 2 * 2;
-        a.edge_row = extra->edge_row; a.edge_col = extra->edge_col;
+        a.edge_row = extra->edge_row; a.edge_col = extra->edge_col; a.crop = extra->crop;
     }
     launch_pair<2>(in, out_paired, a, kb, ((N + 1) / 2) * Cn, stream);
 }

@@ -127,6 +127,14 @@ dau_status_t dau_backward(dau_handle_t* h, const float* bottom, const float* top
     });
 }
 
+dau_status_t dau_get_output_size(dau_handle_t* h, int* h_out, int* w_out) {
+    if (!h || !h_out || !w_out) return fail(DAU_ERR_INVALID_ARGUMENT, "dau_get_output_size: NULL argument");
+    return guarded([&] {
+        DAU_CHECK(h->layer->H() > 0, 3, "dau_get_output_size called before dau_reshape");
+        *h_out = h->layer->H_out(); *w_out = h->layer->W_out();
+    });
+}
+
 dau_status_t dau_set_activation(dau_handle_t* h, int activation) {
     if (!h) return fail(DAU_ERR_INVALID_ARGUMENT, "dau_set_activation: NULL handle");
     return guarded([&] { h->layer->set_activation(activation); });
@@ -164,7 +172,7 @@ dau_status_t dau_forward_host(dau_handle_t* h, int N, int S, int H, int W, const
         DAU_CUDA_CHECK(cudaSetDevice(l->device()));
         size_t fws = 0, bws = 0;
         l->Reshape(N, S, H, W, &fws, &bws);
-        const size_t nin = (size_t)N * S * H * W, nout = (size_t)N * l->F() * H * W;
+        const size_t nin = (size_t)N * S * H * W, nout = (size_t)N * l->F() * l->H_out() * l->W_out();
         const size_t np = (size_t)S * l->G() * l->F();
         DevBuf dx(nin * 4), dy(nout * 4), dwt(np * 4), dm1(np * 4), dm2(np * 4), dsg(np * 4),
             db(bias ? (size_t)l->F() * 4 : 0), dws(fws);
@@ -187,7 +195,7 @@ dau_status_t dau_backward_host(dau_handle_t* h, int N, int S, int H, int W, cons
         DAU_CUDA_CHECK(cudaSetDevice(l->device()));
         size_t fws = 0, bws = 0;
         l->Reshape(N, S, H, W, &fws, &bws);
-        const size_t nin = (size_t)N * S * H * W, nout = (size_t)N * l->F() * H * W;
+        const size_t nin = (size_t)N * S * H * W, nout = (size_t)N * l->F() * l->H_out() * l->W_out();
         const size_t np = (size_t)S * l->G() * l->F();
         DevBuf dx(nin * 4), de(nout * 4), dwt(np * 4), dm1(np * 4), dm2(np * 4), dsg(np * 4),
             gdx(nin * 4), gw(np * 4), gm1(np * 4), gm2(np * 4), gsg(np * 4), gb((size_t)l->F() * 4), dws(bws);

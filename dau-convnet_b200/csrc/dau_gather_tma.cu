@@ -66,6 +66,7 @@ struct TGatherParams {
     int stage_bytes;       // tile + records, multiple of 128
     int debug;
     int relu;              // epilogue: store max(0, y + bias)  
+    int crop;              // `out` is [.., H-2crop, W-2crop]: the centre of the same-size result (pad < (ks-1)/2)
     Mosaic m;              // N, H, W above are the mosaic extents; `out` is the real NCHW tensor
 };
 
@@ -177,8 +178,9 @@ dau_gather_tma_kernel(const __grid_constant__ CUtensorMap in_map, const TGatherP
     const int xs = x0 + lx * C;
     const int H = p.H, W = p.W;
     const bool ident = p.m.kx == 1 && p.m.ky == 1;
-    const bool vec = ident && ((W & 3) == 0) && (xs + C <= W);
-    const size_t rplane = (size_t)p.m.H * p.m.W;
+    const int crop = p.crop, RH = p.m.H - 2 * crop, RW = p.m.W - 2 * crop;
+    const bool vec = ident && crop == 0 && ((W & 3) == 0) && (xs + C <= W);
+    const size_t rplane = (size_t)RH * RW;
 #pragma unroll
     for (int img = 0; img < 2; ++img) {
         const int n = 2 * np + img;
@@ -193,22 +195,20 @@ dau_gather_tma_kernel(const __grid_constant__ CUtensorMap in_map, const TGatherP
                 v[c] = (img == 0 ? acc[r][c].x : acc[r][c].y) + bv;
                 if (p.relu) v[c] = fmaxf(v[c], 0.f);
             }
-            if (ident) {
+            if (vec) {
                 float* orow = p.out + ((size_t)n * p.Cout + co) * rplane + (size_t)y * W;
-                if (vec) {
-                    *reinterpret_cast<float4*>(orow + xs) = make_float4(v[0], v[1], v[2], v[3]);
-                } else {
-#pragma unroll
-                    for (int c = 0; c < C; ++c)
-                        if (xs + c < W) orow[xs + c] = v[c];
-                }
+                *reinterpret_cast<float4*>(orow + xs) = make_float4(v[0], v[1], v[2], v[3]);
             } else {
-                // mosaic: gap pixels and cells beyond the batch are computed but never stored
+                // mosaic: gap pixels and cells beyond the batch are computed but never stored;
+                // crop: neither is the border of the same-size result
 #pragma unroll
                 for (int c = 0; c < C; ++c) {
-                    int rn, ry, rx;
-                    if (xs + c < W && mosaic_to_real(p.m, n, y, xs + c, &rn, &ry, &rx))
-                        p.out[((size_t)rn * p.Cout + co) * rplane + (size_t)ry * p.m.W + rx] = v[c];
+                    int rn = n, ry = y, rx = xs + c;
+                    bool ok = xs + c < W;
+                    if (ok && !ident) ok = mosaic_to_real(p.m, n, y, xs + c, &rn, &ry, &rx);
+                    ry -= crop; rx -= crop;
+                    if (ok && ry >= 0 && ry < RH && rx >= 0 && rx < RW)
+                        p.out[((size_t)rn * p.Cout + co) * rplane + (size_t)ry * RW + rx] = v[c];
                 }
             }
         }
@@ -274,7 +274,7 @@ bool plan_gather_tma(int N, int Cin, int Cout, int G, int H, int W, int max_off,
 }
 
 void launch_gather_tma(const GatherPlan& plan, const float* in_paired, const UnitRec* table, const float* bias,
-                       float* out, const Mosaic& m, int Cin, int Cout, int G, cudaStream_t stream, int relu) {
+                       float* out, const Mosaic& m, int Cin, int Cout, int G, cudaStream_t stream, int relu, int crop) {
     const int N = m.Nv, H = m.Hv, W = m.Wv;
     // tensor map of the paired gather layout: dims (q*2+i, p, y, plane)
     const uint64_t qv = (W + 3) / 4, qp = (qv + 1) / 2 * 2;
@@ -288,7 +288,7 @@ void launch_gather_tma(const GatherPlan& plan, const float* in_paired, const Uni
     p.N = N; p.Cin = Cin; p.Cout = Cout; p.G = G; p.H = H; p.W = W;
     p.tiles_x = (W + TW - 1) / TW; p.nstage = plan.nstage;
     p.stage_bytes = plan.stage_words * 4;
-    p.m = m; p.relu = relu;
+    p.m = m; p.relu = relu; p.crop = crop;
     p.debug = getenv("DAU_DEBUG") ? atoi(getenv("DAU_DEBUG")) : 0;
     switch (plan.variant) {
         case 0: launch_t<4>(plan, map, p, stream); break;

@@ -67,7 +67,8 @@ void HostPipeline::step(int N, int S, int H, int W, int chunk, float sigma_hint,
     DAU_CUDA_CHECK(cudaSetDevice(device_));
     chunk = std::min(chunk, N);
     const int F = st_.num_output;
-    const size_t in_img = (size_t)S * H * W, out_img = (size_t)F * H * W;
+    const int crop = (st_.kernel_size - 1) / 2 - st_.pad;             // top is [N, F, H-2crop, W-2crop]
+    const size_t in_img = (size_t)S * H * W, out_img = (size_t)F * (H - 2 * crop) * (W - 2 * crop);
     auto up = [](size_t v) { return (v + 255) / 256 * 256; };
 
     // chunk schedule: short chunks at both ends (the first copy-in and the last copy-out are the

@@ -90,13 +90,16 @@ struct GatherPlan {            // chosen once per shape by plan_gather_tma()
 size_t paired_layout_floats(int N, int Cn, int H, int W);
 bool plan_gather_tma(int N, int Cin, int Cout, int G, int H, int W, int max_off, GatherPlan* out);
 void launch_gather_tma(const GatherPlan& p, const float* in_paired, const UnitRec* table, const float* bias,
-                       float* out, const Mosaic& m, int Cin, int Cout, int G, cudaStream_t stream, int relu = 0);
+                       float* out, const Mosaic& m, int Cin, int Cout, int G, cudaStream_t stream, int relu = 0,
+                       int crop = 0);
 // Extras of the top-error blur (the prologue fused into the error load)
 struct ErrorSideArgs {
     const float* mask = nullptr;   // activation output, same shape as the error: error := 0 where mask <= 0
     float* sgp = nullptr;          // also write the (masked) un-blurred error in the SGP layout of the
                                    // gradient kernel, i.e. what launch_error_relayout produces
     int edge_row = 0, edge_col = 0;// ignore_edge_gradients mask of the SGP copy
+    int crop = 0;                  // the error (and mask) tensors are [.., H-2crop, W-2crop] and sit at offset
+                                   // (crop, crop) of the full grid, zeros around (base_dau_conv_layer.cu:258-266)
 };
 void launch_blur_single_paired(const float* in, float* out_paired, const Mosaic& m, int Cn, int kb,
                                const float* fx, const float* fy, cudaStream_t stream,
@@ -130,7 +133,7 @@ void launch_grad_tma(const GradPlan& p, const float* xk_strips, const float* err
 void launch_blur_bank_strips(const float* in, float* out_strips, const Mosaic& m, int S,
                              const BlurFactors& f, cudaStream_t stream);
 void launch_error_relayout(const float* err, float* out_sg, const Mosaic& m, int F, int mask_row, int mask_col,
-                           cudaStream_t stream, const float* act_mask = nullptr);
+                           cudaStream_t stream, const float* act_mask = nullptr, int crop = 0);
 
 struct GradFinalizeArgs {
     const float* partial; int n_splits;

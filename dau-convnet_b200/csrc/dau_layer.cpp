@@ -73,7 +73,10 @@ DAUConvLayerB200::DAUConvLayerB200(const dau_settings_t& s, int device) : st_(s)
     DAU_CHECK(s.stride == 1, 4, "DAUConvolution current supports only stride == 1");   // .cpp:68-69
     DAU_CHECK(s.kernel_size >= 3 && (s.kernel_size & 1) == 1, 1, "kernel_size must be odd and >= 3");
     DAU_CHECK(s.kernel_size / 2 <= 32, 4, "kernel_size above 65 is not supported (dau_conv_op.cpp:250-253)");
-    DAU_CHECK(s.pad == (s.kernel_size - 1) / 2, 4, "only pad == (kernel_size-1)/2 is supported (output size == input size)");
+    // pad < (ks-1)/2: the output is the centre [H-2crop, W-2crop] of the same-size result
+    // (height_out_ = H + 2*pad - ks + 1, base_dau_conv_layer.cpp:20-22; border = H/2 - H_out/2, :544-545)
+    crop_ = (s.kernel_size - 1) / 2 - s.pad;
+    DAU_CHECK(s.pad >= 0 && crop_ >= 0, 4, "pad must be in [0, (kernel_size-1)/2] (output never larger than the input)");
     DAU_CHECK(s.offsets_already_centered != 0, 4, "only centred offsets are supported");
     G_ = s.number_units_x * s.number_units_y;
     DAU_CHECK(s.number_units_ignore >= 0 && s.number_units_ignore < G_ + 1, 1, "number_units_ignore out of range");
@@ -93,6 +96,7 @@ DAUConvLayerB200::~DAUConvLayerB200() {
 
 void DAUConvLayerB200::Reshape(int N, int S, int H, int W, size_t* fwd_ws, size_t* bwd_ws) {
     DAU_CHECK(N > 0 && S > 0 && H > 0 && W > 0, 1, "bottom shape must be a positive 4-D NCHW shape");
+    DAU_CHECK(H > 2 * crop_ && W > 2 * crop_, 1, "input smaller than kernel_size - 2*pad: empty output");
     N_ = N; S_ = S; H_ = H; W_ = W;
     const size_t units = (size_t)S * G_ * F_;
     // TMA + FFMA2 kernels on the (mosaic) pair layouts
@@ -235,7 +239,7 @@ void DAUConvLayerB200::Forward_gpu(const float* bottom, float* w, float* mu1, fl
 
     tic(0, 3, stream);
     launch_gather_tma(fwd_plan_, xb, table, st_.bias_term ? bias : nullptr, top, mosaic_, S_, F_, G_, stream,
-                      activation_ == DAU_ACT_RELU ? 1 : 0);
+                      activation_ == DAU_ACT_RELU ? 1 : 0, crop_);
     toc(0, 3, stream);
 }
 
@@ -285,21 +289,21 @@ void DAUConvLayerB200::Backward_gpu(const float* bottom, const float* top_error,
         launch_unit_prep(ua, nullptr, want_input ? btable : nullptr, want_params ? gtable : nullptr, flag, stream);
         toc(1, 1, stream);
     }
-    const int mrow = st_.ignore_edge_gradients && edge_rule(H_) ? 1 : 0;
-    const int mcol = st_.ignore_edge_gradients && edge_rule(W_) ? 1 : 0;
+    const int mrow = st_.ignore_edge_gradients && edge_rule(H_out()) ? 1 : 0;
+    const int mcol = st_.ignore_edge_gradients && edge_rule(W_out()) ? 1 : 0;
     if (want_input) {
         // blur the error with the rotated filter (base_dau_conv_layer.cu:278-288); the same kernel
         // hands the un-blurred tile to the gradient kernel in its own layout, so the error is read
         // from HBM once
         tic(1, 4, stream);
         ErrorSideArgs ex;
-        ex.mask = act; ex.sgp = want_params ? esg : nullptr; ex.edge_row = mrow; ex.edge_col = mcol;
+        ex.mask = act; ex.sgp = want_params ? esg : nullptr; ex.edge_row = mrow; ex.edge_col = mcol; ex.crop = crop_;
         launch_blur_single_paired(top_error, eb, mosaic_, F_, f.kb, f.err_x, f.err_y, stream, &ex);
         toc(1, 4, stream);
     }
     if (want_params) {
         tic(1, 2, stream);
-        if (!want_input) launch_error_relayout(top_error, esg, mosaic_, F_, mrow, mcol, stream, act);
+        if (!want_input) launch_error_relayout(top_error, esg, mosaic_, F_, mrow, mcol, stream, act, crop_);
         launch_grad_tma(grad_plan_, xk, esg, gtable, partial, mosaic_.Nv, S_, F_, G_, mosaic_.Hv, mosaic_.Wv, stream);
         toc(1, 2, stream);
         tic(1, 3, stream);
@@ -322,7 +326,7 @@ void DAUConvLayerB200::Backward_gpu(const float* bottom, const float* top_error,
     }
     if ((flags & DAU_GRAD_BIAS) && st_.bias_term && dbias) {
         tic(1, 6, stream);
-        launch_bias_grad(top_error, act, dbias, N_, F_, H_ * W_, stream);
+        launch_bias_grad(top_error, act, dbias, N_, F_, H_out() * W_out(), stream);
         toc(1, 6, stream);
     }
 }

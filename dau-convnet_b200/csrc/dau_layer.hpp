@@ -51,6 +51,8 @@ public:
 
     int N() const { return N_; } int S() const { return S_; } int F() const { return F_; }
     int G() const { return G_; } int H() const { return H_; } int W() const { return W_; }
+    // top / top_error are [N, F, H_out, W_out]
+    int H_out() const { return H_ - 2 * crop_; } int W_out() const { return W_ - 2 * crop_; }
     int device() const { return device_; }
     const dau_settings_t& settings() const { return st_; }
     const GatherPlan& fwd_plan() const { return fwd_plan_; }
@@ -75,6 +77,7 @@ private:
     size_t off_bwd_xk_ = 0, off_bwd_esg_ = 0, off_bwd_eb_ = 0, off_bwd_table_ = 0, off_bwd_gtable_ = 0,
            off_bwd_partial_ = 0, off_bwd_flag_ = 0;
     int activation_ = 0;
+    int crop_ = 0;             // (kernel_size-1)/2 - pad
     float sigma_hint_ = 0.f;
     float cached_sigma_ = -1.f;
     BlurFactors factors_{};

@@ -11,16 +11,17 @@ namespace {
 __global__ void __launch_bounds__(256) error_relayout_kernel(const float* __restrict__ err, float2* __restrict__ out,
                                                              const __grid_constant__ Mosaic m, int F, int qp,
                                                              int mask_row, int mask_col,
-                                                             const float* __restrict__ act) {
+                                                             const float* __restrict__ act, int crop) {
     const int pf = blockIdx.x;                            // (pair, feature)
     const int np = pf / F, f = pf - np * F;
     const int idx = blockIdx.y * 256 + threadIdx.x;       // (row, column pair) of the mosaic plane
     const int vy = idx / qp, j = idx - vy * qp;
     if (vy >= m.Hv) return;
     float2* dst = out + ((size_t)pf * m.Hv + vy) * 2 * qp;
-    const size_t rplane = (size_t)m.H * m.W;
+    const int RH = m.H - 2 * crop, RW = m.W - 2 * crop;   // the error tensor sits at (crop, crop) of the full grid
+    const size_t rplane = (size_t)RH * RW;
     float v[2][2] = {{0.f, 0.f}, {0.f, 0.f}};             // [column 2j / 2j+1][image of the pair]
-    if (m.kx == 1 && m.ky == 1 && (m.W & 1) == 0) {
+    if (m.kx == 1 && m.ky == 1 && (m.W & 1) == 0 && crop == 0) {
         // identity mosaic, even width: one float2 load per image
         const int x = 2 * j;
         if (x < m.W && !(mask_row && vy == m.H - 1)) {
@@ -46,8 +47,10 @@ __global__ void __launch_bounds__(256) error_relayout_kernel(const float* __rest
                 const int vx = 2 * j + c, nv = 2 * np + img;
                 int rn, ry, rx;
                 if (vx < m.Wv && nv < m.Nv && mosaic_to_real(m, nv, vy, vx, &rn, &ry, &rx)) {
-                    const bool dead = (mask_row && ry == m.H - 1) || (mask_col && rx == m.W - 1);
-                    const size_t at = ((size_t)rn * F + f) * rplane + (size_t)ry * m.W + rx;
+                    ry -= crop; rx -= crop;
+                    if (ry < 0 || ry >= RH || rx < 0 || rx >= RW) continue;
+                    const bool dead = (mask_row && ry == RH - 1) || (mask_col && rx == RW - 1);
+                    const size_t at = ((size_t)rn * F + f) * rplane + (size_t)ry * RW + rx;
                     if (!dead && !(act && !(__ldg(act + at) > 0.f))) v[c][img] = __ldg(err + at);
                 }
             }
@@ -58,13 +61,13 @@ __global__ void __launch_bounds__(256) error_relayout_kernel(const float* __rest
 }  // namespace
 
 void launch_error_relayout(const float* err, float* out_sg, const Mosaic& m, int F, int mask_row, int mask_col,
-                           cudaStream_t stream, const float* act_mask) {
+                           cudaStream_t stream, const float* act_mask, int crop) {
     const int qv = (m.Wv + 1) / 2, qp = (qv + 1) / 2 * 2;
     const long long total = (long long)((m.Nv + 1) / 2) * F;
     const int blocks_y = (m.Hv * qp + 255) / 256;
     DAU_CHECK(total < (1LL << 31) && blocks_y <= 65535, 4, "shape too large for the error re-layout grid");
     error_relayout_kernel<<<dim3((unsigned)total, blocks_y), 256, 0, stream>>>(err, reinterpret_cast<float2*>(out_sg), m, F, qp,
-                                                                           mask_row, mask_col, act_mask);
+                                                                           mask_row, mask_col, act_mask, crop);
     DAU_CUDA_CHECK(cudaGetLastError());
 }
 

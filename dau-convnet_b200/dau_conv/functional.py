@@ -87,6 +87,9 @@ class DAULayerHandle(object):
             _lib.check(_lib.lib.dau_reshape(self._h, N, S, H, W, C.byref(f), C.byref(b)))
             self.fwd_bytes, self.bwd_bytes = f.value, b.value
             self._shape = (N, S, H, W, self._hint)
+            ho, wo = C.c_int(0), C.c_int(0)
+            _lib.check(_lib.lib.dau_get_output_size(self._h, C.byref(ho), C.byref(wo)))
+            self.out_hw = (ho.value, wo.value)      # == (H, W) unless pad < (kernel_size-1)/2
 
     def workspace(self, nbytes):
         if self._ws is None or self._ws.numel() < nbytes:
@@ -124,7 +127,7 @@ class DAULayerHandle(object):
         self.set_activation(activation)
         F = self.settings.num_output
         if out is None:
-            out = torch.empty((N, F, H, W), dtype=torch.float32, device=x.device)
+            out = torch.empty((N, F) + self.out_hw, dtype=torch.float32, device=x.device)
         ws = self.workspace(self.fwd_bytes)
         stream = torch.cuda.current_stream(x.device).cuda_stream
         _lib.check(_lib.lib.dau_forward(
@@ -141,6 +144,9 @@ class DAULayerHandle(object):
         N, S, H, W = x.shape
         self.reshape(N, S, H, W)
         self.set_activation(activation)
+        if tuple(top_error.shape) != (N, self.settings.num_output) + self.out_hw:
+            raise RuntimeError("DAUConvGrad: grad has shape %s, expected %s" % (
+                tuple(top_error.shape), (N, self.settings.num_output) + self.out_hw))
         dx = torch.empty_like(x) if flags & _lib.GRAD_INPUT else None
         if grads is None:
             grads = [torch.zeros_like(w) for _ in range(4)]     # the TF op pre-zeroes (grad_op.cpp:202-205)

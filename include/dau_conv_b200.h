@@ -97,13 +97,19 @@ dau_status_t dau_reshape(dau_handle_t* h, int N, int S, int H, int W,
  * value <= 0 re-enables the read. */
 dau_status_t dau_set_sigma_hint(dau_handle_t* h, float value);
 
-/* top[N,F,H,W] = DAU(bottom[N,S,H,W]); top is overwritten. bias_dev may be NULL. */
+/* Output size after dau_reshape: H_out = H + 2*pad - kernel_size + 1 (base_dau_conv_layer.cpp:20-22).
+ * pad == (kernel_size-1)/2 (what the TF op always passes) gives H_out == H; a smaller pad gives the
+ * centre of the same-size result, and the backward pass takes top_error[N,F,H_out,W_out] as if
+ * zero-padded back to H x W (base_dau_conv_layer.cu:258-266).  pad > (kernel_size-1)/2 is refused. */
+dau_status_t dau_get_output_size(dau_handle_t* h, int* h_out, int* w_out);
+
+/* top[N,F,H_out,W_out] = DAU(bottom[N,S,H,W]); top is overwritten. bias_dev may be NULL. */
 dau_status_t dau_forward(dau_handle_t* h, const float* bottom_dev,
                          float* w_dev, float* mu1_dev, float* mu2_dev, float* sigma_dev,
                          const float* bias_dev, float* top_dev,
                          void* workspace_dev, size_t workspace_bytes, void* stream);
 
-/* bottom_error[N,S,H,W] is overwritten; d{w,mu1,mu2,sigma}[1,S,G,F] (and dbias[F]) are
+/* top_error is [N,F,H_out,W_out]; bottom_error[N,S,H,W] is overwritten; d{w,mu1,mu2,sigma}[1,S,G,F] (and dbias[F]) are
  * ACCUMULATED INTO (caller pre-zeroes, dau_conv_grad_op.cpp:202-205).  dmu1/dmu2/dsigma
  * carry the xw factor, dmu1/dmu2 also mu_learning_rate_factor, NaNs in dmu are zeroed. */
 dau_status_t dau_backward(dau_handle_t* h, const float* bottom_dev, const float* top_error_dev,

@@ -18,6 +18,7 @@ What it follows (paths relative to /root/reference):
   * correlation convention .......... src/dau_conv/util/convolve.cu:107-129
   * edge masks (ignore_edge_grads) .. dau_conv_test.py:110-136, base_dau_conv_layer.cpp:754-791
   * x w post-scaling of mu/sigma .... base_dau_conv_layer.cu:335-337, dau_conv_test.py:289-292
+  * pad < (ks-1)/2 (output smaller) .. base_dau_conv_layer.cpp:20-22, 544-545, 938-949; .cu:258-266
 
 All arithmetic is float64 unless ``dtype`` says otherwise; callers cast.
 Tensor layouts are the reference's: x [N,S,H,W], w/mu1/mu2 [1,S,G,F] (F fastest).
@@ -31,6 +32,7 @@ import numpy as np
 __all__ = [
     "blur_kernel_size", "get_filters", "correlate_same", "offset_and_sum",
     "offset_and_dot", "edge_mask_flags", "forward", "backward",
+    "output_border", "forward_cropped", "backward_cropped",
 ]
 
 
@@ -231,3 +233,45 @@ def backward(x, error, w, mu1, mu2, sigma, num_dau_units_ignore=0, ignore_edge_g
                                     ignore_edge_gradients, use_interpolation))
     wv = np.asarray(w, dtype=np.float64)
     return dx, grads[0], grads[1] * wv, grads[2] * wv, grads[3] * wv
+
+
+def output_border(size_in, kernel_size, pad):
+    """(border, size_out): size_out = size_in + 2*pad - kernel_size + 1 (base_dau_conv_layer.cpp:20-22,
+    stride 1) and the output pixel o sits over input pixel o + border with
+    border = size_in/2 - size_out/2 (base_dau_conv_layer.cpp:544-545)."""
+    size_out = size_in + 2 * pad - kernel_size + 1
+    return size_in // 2 - size_out // 2, size_out
+
+
+def forward_cropped(x, w, mu1, mu2, sigma, kernel_size, pad, **kw):
+    """Forward with pad < (kernel_size-1)/2: the centre [H_out, W_out] of the same-size result
+    (the reference's kernels compute exactly those pixels, base_dau_conv_layer.cpp:540-545)."""
+    y = forward(x, w, mu1, mu2, sigma, **kw)
+    by, ho = output_border(y.shape[2], kernel_size, pad)
+    bx, wo = output_border(y.shape[3], kernel_size, pad)
+    return y[:, :, by:by + ho, bx:bx + wo]
+
+
+def backward_cropped(x, error, w, mu1, mu2, sigma, kernel_size, pad, ignore_edge_gradients=True, **kw):
+    """Backward for an error of the OUTPUT size: the reference zero-pads it back to the input size
+    at offset `border` (caffe_gpu_pad2d, base_dau_conv_layer.cu:258-266; im2col padding
+    base_dau_conv_layer.cpp:938-949) and runs the same-size pass; the edge mask of
+    ignore_edge_gradients is taken on the OUTPUT grid (base_dau_conv_layer.cpp:763-791) and
+    touches the parameter gradients only."""
+    x = np.asarray(x, dtype=np.float64)
+    error = np.asarray(error, dtype=np.float64)
+    N, S, H, W = x.shape
+    by, ho = output_border(H, kernel_size, pad)
+    bx, wo = output_border(W, kernel_size, pad)
+    assert error.shape[2:] == (ho, wo), (error.shape, ho, wo)
+    full = np.zeros(error.shape[:2] + (H, W), dtype=np.float64)
+    full[:, :, by:by + ho, bx:bx + wo] = error
+    dx = backward(x, full, w, mu1, mu2, sigma, ignore_edge_gradients=False, **kw)[0]
+    if ignore_edge_gradients:
+        last_row, last_col = edge_mask_flags(ho, wo)
+        if last_col:
+            full[:, :, :, bx + wo - 1] = 0.0
+        if last_row:
+            full[:, :, by + ho - 1, :] = 0.0
+    grads = backward(x, full, w, mu1, mu2, sigma, ignore_edge_gradients=False, **kw)[1:]
+    return (dx,) + tuple(grads)

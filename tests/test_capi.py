@@ -100,6 +100,6 @@ def test_create_without_gpu_fails_loudly(dau_conv):
 def test_invalid_settings_rejected_before_touching_the_device(dau_conv):
     h = C.c_void_p()
     lib = dau_conv._lib.lib
-    for bad in ({"stride": 2}, {"kernel_size": 8}, {"pad": 1}, {"num_output": 0}, {"kernel_size": 67, "pad": 33}):
+    for bad in ({"stride": 2}, {"kernel_size": 8}, {"pad": 5}, {"pad": -1}, {"num_output": 0}, {"kernel_size": 67, "pad": 33}):
         st = lib.dau_create(C.byref(dau_conv.default_settings(**bad)), 0, C.byref(h))
         assert st in (1, 4), bad

@@ -341,3 +341,38 @@ def test_fused_activation_needs_top_data_and_none_equals_plain_backward():
     with pytest.raises(dau_conv.DAUError):
         h.set_activation(7)
     h.set_activation(_lib.ACT_NONE)
+
+
+# ---- row f4: pad < (kernel_size-1)/2, output smaller than the input --------------------------------
+CROP_SHAPES = [
+    # (N, W, H, S, F, units, kernel, pad, mu_range)
+    (4, 64, 64, 4, 8, (1, 2), 9, 2, 3),        # identity mosaic; crop 2 -> 60 x 60
+    (3, 40, 24, 3, 5, (2, 2), 9, 0, 3.9),      # "valid" output 32 x 16, odd batch
+    (6, 13, 13, 4, 6, (1, 2), 9, 3, 3),        # mosaic; 11 x 11
+    (2, 48, 48, 2, 4, (1, 2), 17, 4, 6),       # crop 4 -> 40 x 40: the edge rule fires on the OUTPUT size
+]
+
+
+@pytest.mark.parametrize("shape", CROP_SHAPES, ids=["x".join(str(v) for v in s[:5]) + "_k%d_p%d" % (s[6], s[7])
+                                                    for s in CROP_SHAPES])
+@pytest.mark.parametrize("edge", [True, False], ids=["edgemask", "exact"])
+def test_output_smaller_than_input(shape, edge):
+    N, W, H, S, F, units, ks, pad, m = shape
+    x, _, w, mu1, mu2, _ = _case((N, W, H, S, F, units, ks, m), 41)
+    by, ho = O.output_border(H, ks, pad)
+    bx, wo = O.output_border(W, ks, pad)
+    assert by == (ks - 1) // 2 - pad and ho == H - 2 * by and wo == W - 2 * bx
+    err = np.random.default_rng(8).standard_normal((N, F, ho, wo)).astype(np.float32)
+    y, g = run_layer(x, err, w, mu1, mu2, 0.5, ks, pad=pad, number_units_x=units[0], number_units_y=units[1],
+                     unit_testing=edge)
+    assert y.shape == (N, F, ho, wo) and g[0].shape == x.shape
+    close(y, O.forward_cropped(x, w, mu1, mu2, [0.5], ks, pad), "y")
+    ref = O.backward_cropped(x, err, w, mu1, mu2, [0.5], ks, pad, ignore_edge_gradients=edge)
+    for name, a, b in zip(["dx", "dw", "dmu1", "dmu2", "dsigma"], g, ref):
+        close(a, b, name, scale_atol=name != "dx")
+
+
+def test_pad_larger_than_same_is_refused():
+    import dau_conv
+    with pytest.raises(dau_conv.DAUError):
+        dau_conv.get_handle("cuda:0", num_output=4, kernel_size=9, pad=5)
