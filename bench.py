@@ -255,7 +255,7 @@ def run_ours(args, rank, world, local_rank):
     dxp = torch.empty((N, S, H, W), dtype=torch.float32).pin_memory()
     gp = torch.empty((4, 1, S, G, F), dtype=torch.float32).pin_memory()
 
-    e2e_chunk = args.e2e_chunk if args.e2e_chunk > 0 else max(8, N // 4)
+    e2e_chunk = args.e2e_chunk if args.e2e_chunk > 0 else max(8, N // 2)
 
     def e2e_step():
         # the public host-buffer call: chunked H2D -> fwd+bwd -> D2H, copies overlapped with kernels
@@ -298,7 +298,7 @@ def run_ours(args, rank, world, local_rank):
                    "l2": "inputs larger than L2 (x and top_error are %.0f MB each; L2 is 126 MB)" % (xh.nbytes / 1e6)},
         "roofline": roofline, "cpu_baseline": cpu_baseline,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "steps": e2e_steps, "chunk_images": e2e_chunk,
+                "steps": e2e_steps, "max_chunk_images": e2e_chunk,
                 "what": "dau_train_step_host: pinned host x, top_error -> device; fwd+bwd; y, dL/dx and the "
                         "4 parameter gradients -> pinned host; copies overlapped with the kernels chunk by chunk"},
         "gpu_launches": launches, "clocks": sampler.summary() if sampler else None,
@@ -317,7 +317,8 @@ def main():
                          "on C2; a quarter of it per step for --impl reference)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--e2e-chunk", type=int, default=0,
-                    help="images per chunk of the host-buffer step (0: a quarter of the per-GPU batch)")
+                    help="largest chunk of the host-buffer step in images (0: half the per-GPU batch); the library "
+                         "searches the chunk schedule under this cap")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

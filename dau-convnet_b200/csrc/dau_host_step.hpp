@@ -4,6 +4,7 @@
 #include "dau_layer.hpp"
 
 #include <map>
+#include <vector>
 
 namespace dau {
 
@@ -22,12 +23,14 @@ public:
 
 private:
     DAUConvLayerB200* layer_for(int n, int S, int H, int W, float sigma_hint, size_t* fws, size_t* bws);
+    const std::vector<int>& schedule(int N, int S, int H, int W, int cap, float sigma_hint, bool want_dx);
 
     dau_settings_t st_;
     int device_;
     std::map<int, DAUConvLayerB200*> layers_;      // one planned layer per chunk size
+    std::map<std::vector<int>, std::vector<int>> schedules_;   // (N,S,H,W,cap,dx) -> chunk sizes
     cudaStream_t s_in_ = nullptr, s_comp_ = nullptr, s_out_ = nullptr;
-    cudaEvent_t in_done_[2], comp_done_[2], out_done_[2], fork_;
+    cudaEvent_t in_done_[2], comp_done_[2], out_done_[2], x_done_[2], fwd_done_[2], fork_;
     void* pool_ = nullptr;                          // staging buffers + layer workspace
     size_t pool_bytes_ = 0;
 };

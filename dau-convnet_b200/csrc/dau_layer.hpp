@@ -56,7 +56,9 @@ public:
     int device() const { return device_; }
     const dau_settings_t& settings() const { return st_; }
     const GatherPlan& fwd_plan() const { return fwd_plan_; }
+    const GatherPlan& bwd_plan() const { return bwd_plan_; }
     const GradPlan& grad_plan() const { return grad_plan_; }
+    int num_sms() const { return num_sms_; }
     const Mosaic& mosaic() const { return mosaic_; }
 
 private:

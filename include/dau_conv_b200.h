@@ -152,8 +152,10 @@ dau_status_t dau_backward_host(dau_handle_t* h, int N, int S, int H, int W, cons
                                unsigned flags);
 
 /* One training step (dau_forward + dau_backward, all gradients) on a batch that lives in HOST
- * memory, cut into chunks of `chunk_images` whose PCIe copies overlap the kernels of the
- * neighbouring chunks (three internal streams, double-buffered staging owned by the handle).
+ * memory, cut into chunks of at most `chunk_images` whose PCIe copies overlap the kernels of the
+ * neighbouring chunks (three internal streams, double-buffered staging owned by the handle; the
+ * chunk sizes -- short at both ends, where nothing can hide a copy -- are searched per shape
+ * against a model of the streams and of the kernels' last-wave fill).
  * x, top_error, y, dx: host pointers, NCHW fp32 (pinned memory for real overlap; y / dx may be
  * NULL).  Parameters and parameter gradients: DEVICE pointers [1,S,G,F]; the gradients are
  * accumulated into, as in dau_backward.  Stream-ordered with respect to `stream`, asynchronous
