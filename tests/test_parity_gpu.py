@@ -376,3 +376,55 @@ def test_pad_larger_than_same_is_refused():
     import dau_conv
     with pytest.raises(dau_conv.DAUError):
         dau_conv.get_handle("cuda:0", num_output=4, kernel_size=9, pad=5)
+
+
+# ---- seeded random sweep over shapes and flags (the reference's own test draws its cases the same
+#      way, dau_conv_test.py:418-437; this widens it to every attribute the op accepts) -------------
+def _fuzz_cases(count, seed):
+    rng = np.random.default_rng(seed)
+    cases = []
+    for i in range(count):
+        ks = int(rng.choice([3, 5, 9, 9, 17, 33]))
+        pad = (ks - 1) // 2 if rng.random() < 0.7 else int(rng.integers(0, (ks - 1) // 2 + 1))
+        crop = (ks - 1) // 2 - pad
+        H = int(rng.integers(2 * crop + 1, 2 * crop + 40)); W = int(rng.integers(2 * crop + 1, 2 * crop + 80))
+        cases.append(dict(
+            N=int(rng.integers(1, 8)), H=H, W=W, S=int(rng.integers(1, 10)), F=int(rng.integers(1, 12)),
+            ux=int(rng.integers(1, 3)), uy=int(rng.integers(1, 4)), ks=ks, pad=pad,
+            sigma=float(rng.choice([0.4, 0.5, 0.5, 0.65, 0.8, 1.0])),
+            attrs=dict(unit_testing=bool(rng.integers(0, 2)), use_interpolation=bool(rng.random() < 0.8),
+                       single_dim_kernel=bool(rng.random() < 0.15), forbid_positive_dim1=bool(rng.random() < 0.15),
+                       square_unit_normalization=bool(rng.random() < 0.2), unit_normalization=bool(rng.random() < 0.85),
+                       number_units_ignore=int(rng.integers(0, 2))),
+            seed=1000 + i))
+    return cases
+
+
+@pytest.mark.parametrize("case", _fuzz_cases(100, 2024), ids=lambda c: "N%dx%dx%dx%d_F%d_G%d_k%d_p%d_s%g" % (
+    c["N"], c["S"], c["H"], c["W"], c["F"], c["ux"] * c["uy"], c["ks"], c["pad"], c["sigma"]))
+def test_random_shapes_and_flags(case):
+    c = case
+    G = c["ux"] * c["uy"]
+    a = dict(c["attrs"])
+    a["number_units_ignore"] = min(a["number_units_ignore"], G - 1)
+    rng = np.random.default_rng(c["seed"])
+    x = rng.random((c["N"], c["S"], c["H"], c["W"])).astype(np.float32)
+    w = (0.1 * rng.standard_normal((1, c["S"], G, c["F"]))).astype(np.float32)
+    lim = c["ks"] // 2 - 0.01
+    mu1 = rng.uniform(-lim, lim, w.shape).astype(np.float32)
+    mu2 = rng.uniform(-lim, lim, w.shape).astype(np.float32)
+    if a["single_dim_kernel"]:
+        mu2[:] = 0                                      # DAUConv1d pins mu2 (dau_conv.py:560-571)
+    by, ho = O.output_border(c["H"], c["ks"], c["pad"])
+    bx, wo = O.output_border(c["W"], c["ks"], c["pad"])
+    err = rng.standard_normal((c["N"], c["F"], ho, wo)).astype(np.float32)
+    y, g = run_layer(x, err, w, mu1, mu2, c["sigma"], c["ks"], pad=c["pad"], number_units_x=c["ux"],
+                     number_units_y=c["uy"], **a)
+    kw = dict(num_dau_units_ignore=a["number_units_ignore"], single_dim_kernel=a["single_dim_kernel"],
+              forbid_positive_dim1=a["forbid_positive_dim1"], use_interpolation=a["use_interpolation"],
+              unit_normalization=a["unit_normalization"], square_unit_normalization=a["square_unit_normalization"])
+    close(y, O.forward_cropped(x, w, mu1, mu2, [c["sigma"]], c["ks"], c["pad"], **kw), "y")
+    ref = O.backward_cropped(x, err, w, mu1, mu2, [c["sigma"]], c["ks"], c["pad"],
+                             ignore_edge_gradients=a["unit_testing"], **kw)
+    for name, got, want in zip(["dx", "dw", "dmu1", "dmu2", "dsigma"], g, ref):
+        close(got, want, name, scale_atol=name != "dx")
