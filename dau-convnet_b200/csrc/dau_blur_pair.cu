@@ -101,6 +101,23 @@ blur_pair_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
     const bool ident = a.m.kx == 1 && a.m.ky == 1;
     const bool live1 = 2 * np + 1 < a.N;
 
+    // ---- mosaic maps of the tile's rows and columns: (cell index << 16 | pixel inside the cell), or
+    //      -1 for gap pixels and for what lies outside the mosaic.  Integer divisions happen here,
+    //      ROWS + SW times per CTA, and not once per staged element ----------------------------------
+    __shared__ int s_rowmap[ROWS], s_colmap[SW];
+    for (int i = tid; i < ROWS + SW; i += PT_THREADS) {
+        const bool row = i < ROWS;
+        const int v = row ? y0 + i - C : x0 + (i - ROWS) - PADX;
+        const int ext = row ? H : W, pitch = row ? a.m.py : a.m.px, size = row ? a.m.H : a.m.W, cells = row ? a.m.ky : a.m.kx;
+        int code = -1;
+        if (v >= 0 && v < ext) {
+            const int j = v / pitch, l = v - j * pitch;
+            if (l < size && j < cells) code = (j << 16) | l;
+        }
+        if (row) s_rowmap[i] = code; else s_colmap[i - ROWS] = code;
+    }
+    if (!TMA) __syncthreads();                               // (the TMA branch synchronises below)
+
     // ---- stage the haloed tiles of both images -----------------------------------------------------
     if (TMA) {
         if (tid == 0) {
@@ -130,16 +147,11 @@ blur_pair_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
             float* dst = s_in + img * IMG_FLOATS;
             for (int i = tid; i < ROWS * SW; i += PT_THREADS) {
                 const int r = i / SW, q = i - r * SW;
-                const int gy = y0 + r - C, gx = x0 + q - PADX;
-                size_t src = 0;
-                bool ok = n < a.N && gy >= 0 && gy < H && gx >= 0 && gx < W;
-                if (ok) {
-                    int rn = n, ry = gy, rx = gx;
-                    if (!ident) ok = mosaic_to_real(a.m, n, gy, gx, &rn, &ry, &rx);
-                    ry -= crop; rx -= crop;
-                    ok = ok && ry >= 0 && ry < RH && rx >= 0 && rx < RW;
-                    if (ok) src = ((size_t)rn * a.Cn + cn) * rplane + (size_t)ry * RW + rx;
-                }
+                const int rm = s_rowmap[r], cm = s_colmap[q];
+                const int nr = (n * a.m.ky + (rm >> 16)) * a.m.kx + (cm >> 16);     // real image
+                const int ry = (rm & 0xffff) - crop, rx = (cm & 0xffff) - crop;
+                const bool ok = (rm | cm) >= 0 && nr < a.m.N && (unsigned)ry < (unsigned)RH && (unsigned)rx < (unsigned)RW;
+                const size_t src = ok ? ((size_t)nr * a.Cn + cn) * rplane + (size_t)ry * RW + rx : 0;
                 cp_async4_zfill(dst + i, in + src, ok);
                 if (masked) cp_async4_zfill(s_mask + img * IMG_FLOATS + i, a.mask + src, ok);
             }
@@ -227,7 +239,6 @@ blur_pair_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
 
     // ---- column pass: a warp = RY output rows x 64 columns x 2 images; lane = (half p, group g) ----
     const int warp = tid >> 5, lane = tid & 31, p = lane >> 4, g = lane & 15;
-    const int gx = x0 + 4 * g + 2 * p;                       // first of the lane's two pixels
     const bool interior = ident && live1 && x0 + PT_W <= W && y0 + TH <= H;
     for (int yb = warp; yb < TH / RY; yb += PT_THREADS / 32) {
         float2 acc[RY][NOUT][2];
@@ -268,14 +279,14 @@ blur_pair_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
             if (!interior) {
                 // zero what lies outside the image: pad columns / rows of the consumer layouts, the
                 // second image of an odd batch, blur tails inside the mosaic gaps
+                const int rm = s_rowmap[yb * RY + o + C];
 #pragma unroll
                 for (int i = 0; i < 2; ++i) {
-                    bool ok0 = gy < H && gx + i < W, ok1 = ok0 && live1;
-                    if (ok0 && !ident) {
-                        int rn, ry, rx;
-                        ok0 = mosaic_to_real(a.m, 2 * np, gy, gx + i, &rn, &ry, &rx);
-                        ok1 = ok1 && mosaic_to_real(a.m, 2 * np + 1, gy, gx + i, &rn, &ry, &rx);
-                    }
+                    const int cm = s_colmap[4 * g + 2 * p + i + PADX];
+                    const int cell = (rm >> 16) * a.m.kx + (cm >> 16), per = a.m.kx * a.m.ky;
+                    const bool px = (rm | cm) >= 0;
+                    const bool ok0 = px && 2 * np * per + cell < a.m.N;
+                    const bool ok1 = px && (2 * np + 1) * per + cell < a.m.N;
 #pragma unroll
                     for (int k = 0; k < NOUT; ++k) {
                         if (!ok0) acc[o][k][i].x = 0.f;

@@ -28,10 +28,10 @@
 //    dy taps of two neighbouring rows);
 //  * the math is fma.rn.f32x2 (FFMA2): both images of the pair share the unit's weights, so
 //    one instruction issues two FMAs -- the kernel is bound by shared-memory wavefronts
-//    (45 LDS.64 per 128 FFMA2 per lane), not by instruction issue.
+//    (85 LDS.64 per 256 FFMA2 per lane), not by instruction issue.
 //
-// CTA = 8 consumer warps (8 output channels) + 1 producer warp; tile = 16 x 64 pixels x 2
-// images; lane = (lx 0..15, ly 0..1) owning an 8 x 4 strip of both images (64 accumulators).
+// CTA = 8 consumer warps (8 output channels) + a producer warpgroup; tile = 32 x 64 pixels x 2
+// images; lane = (lx 0..15, ly 0..1) owning a 16 x 4 strip of both images (128 accumulators).
 #include "dau_kernels.cuh"
 #include "dau_tma.cuh"
 
@@ -92,6 +92,21 @@ dau_gather_tma_kernel(const __grid_constant__ CUtensorMap in_map, const TGatherP
     if (tid == 0) {
         for (int s = 0; s < nstage; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], NW); }
         fence_barrier_init();
+    }
+    // mosaic maps of the tile's rows and columns for the store: (cell << 16 | pixel inside the
+    // cell), -1 for gap pixels -- the integer divisions happen once per CTA, not once per output
+    __shared__ int s_rowmap[TH], s_colmap[TW];
+    if (tid < TH + TW) {
+        const bool row = tid < TH;
+        const int v = row ? y0 + tid : x0 + tid - TH;
+        const int ext = row ? p.H : p.W, pitch = row ? p.m.py : p.m.px, size = row ? p.m.H : p.m.W,
+                  cells = row ? p.m.ky : p.m.kx;
+        int code = -1;
+        if (v < ext) {
+            const int j = v / pitch, l = v - j * pitch;
+            if (l < size && j < cells) code = (j << 16) | l;
+        }
+        if (row) s_rowmap[tid] = code; else s_colmap[tid - TH] = code;
     }
     __syncthreads();
 
@@ -201,13 +216,13 @@ dau_gather_tma_kernel(const __grid_constant__ CUtensorMap in_map, const TGatherP
             } else {
                 // mosaic: gap pixels and cells beyond the batch are computed but never stored;
                 // crop: neither is the border of the same-size result
+                const int rm = s_rowmap[ly * R + r];
 #pragma unroll
                 for (int c = 0; c < C; ++c) {
-                    int rn = n, ry = y, rx = xs + c;
-                    bool ok = xs + c < W;
-                    if (ok && !ident) ok = mosaic_to_real(p.m, n, y, xs + c, &rn, &ry, &rx);
-                    ry -= crop; rx -= crop;
-                    if (ok && ry >= 0 && ry < RH && rx >= 0 && rx < RW)
+                    const int cm = s_colmap[lx * C + c];
+                    const int rn = (n * p.m.ky + (rm >> 16)) * p.m.kx + (cm >> 16);
+                    const int ry = (rm & 0xffff) - crop, rx = (cm & 0xffff) - crop;
+                    if ((rm | cm) >= 0 && rn < p.m.N && (unsigned)ry < (unsigned)RH && (unsigned)rx < (unsigned)RW)
                         p.out[((size_t)rn * p.Cout + co) * rplane + (size_t)ry * RW + rx] = v[c];
                 }
             }
