@@ -66,9 +66,75 @@ struct TGatherParams {
     int stage_bytes;       // tile + records, multiple of 128
     int debug;
     int relu;              // epilogue: store max(0, y + bias)  
+    int gx, gy;            // items are numbered (pair * gy + channel group) * gx + tile
+    int full_items, split_k;   // items >= full_items are cut into split_k parts of the input-channel loop
+    float2* part;          // partial strips of those parts: [slot][warp][r][c][lane]
     int crop;              // `out` is [.., H-2crop, W-2crop]: the centre of the same-size result (pad < (ks-1)/2)
     Mosaic m;              // N, H, W above are the mosaic extents; `out` is the real NCHW tensor
 };
+
+// Mosaic maps of a tile's rows and columns for the store: (cell << 16 | pixel inside the cell), -1
+// for gap pixels -- the integer divisions happen once per CTA, not once per output.
+__device__ __forceinline__ void build_store_maps(const TGatherParams& p, int x0, int y0, int tid, int* s_rowmap,
+                                                 int* s_colmap) {
+    if (tid < TH + TW) {
+        const bool row = tid < TH;
+        const int v = row ? y0 + tid : x0 + tid - TH;
+        const int ext = row ? p.H : p.W, pitch = row ? p.m.py : p.m.px, size = row ? p.m.H : p.m.W,
+                  cells = row ? p.m.ky : p.m.kx;
+        int code = -1;
+        if (v < ext) {
+            const int j = v / pitch, l = v - j * pitch;
+            if (l < size && j < cells) code = (j << 16) | l;
+        }
+        if (row) s_rowmap[tid] = code; else s_colmap[tid - TH] = code;
+    }
+}
+
+// Epilogue: bias, activation, and the store of a lane's 16 x 4 strip of both images of the pair
+// into the caller's NCHW tensor (float4 per row when the planes allow it).
+__device__ __forceinline__ void store_strip(const TGatherParams& p, const float2 (&acc)[R][C], int np, int co, int lx,
+                                            int ly, int x0, int y0, const int* s_rowmap, const int* s_colmap) {
+    const float bv = p.bias ? __ldg(p.bias + co) : 0.f;
+    const int xs = x0 + lx * C;
+    const int H = p.H, W = p.W;
+    const bool ident = p.m.kx == 1 && p.m.ky == 1;
+    const int crop = p.crop, RH = p.m.H - 2 * crop, RW = p.m.W - 2 * crop;
+    const bool vec = ident && crop == 0 && ((W & 3) == 0) && (xs + C <= W);
+    const size_t rplane = (size_t)RH * RW;
+#pragma unroll
+    for (int img = 0; img < 2; ++img) {
+        const int n = 2 * np + img;
+        if (n >= p.N) break;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int y = y0 + ly * R + r;
+            if (y >= H) continue;
+            float v[C];
+#pragma unroll
+            for (int c = 0; c < C; ++c) {
+                v[c] = (img == 0 ? acc[r][c].x : acc[r][c].y) + bv;
+                if (p.relu) v[c] = fmaxf(v[c], 0.f);
+            }
+            if (vec) {
+                float* orow = p.out + ((size_t)n * p.Cout + co) * rplane + (size_t)y * W;
+                *reinterpret_cast<float4*>(orow + xs) = make_float4(v[0], v[1], v[2], v[3]);
+            } else {
+                // mosaic: gap pixels and cells beyond the batch are computed but never stored;
+                // crop: neither is the border of the same-size result
+                const int rm = s_rowmap[ly * R + r];
+#pragma unroll
+                for (int c = 0; c < C; ++c) {
+                    const int cm = s_colmap[lx * C + c];
+                    const int rn = (n * p.m.ky + (rm >> 16)) * p.m.kx + (cm >> 16);
+                    const int ry = (rm & 0xffff) - crop, rx = (cm & 0xffff) - crop;
+                    if ((rm | cm) >= 0 && rn < p.m.N && (unsigned)ry < (unsigned)RH && (unsigned)rx < (unsigned)RW)
+                        p.out[((size_t)rn * p.Cout + co) * rplane + (size_t)ry * RW + rx] = v[c];
+                }
+            }
+        }
+    }
+}
 
 template <int HALO>
 __global__ void __launch_bounds__(NTHREADS, 1)
@@ -82,10 +148,22 @@ dau_gather_tma_kernel(const __grid_constant__ CUtensorMap in_map, const TGatherP
 
     const int tid = threadIdx.x, lane = tid & 31;
     const int warp = (tid >> 5) - 4;               // consumer warp 0..7; negative: producer warpgroup
-    const int tyi = blockIdx.x / p.tiles_x, txi = blockIdx.x - tyi * p.tiles_x;
+    // item = (tile, group of 8 output channels, image pair).  The items of the last, partial wave are
+    // cut along the input channels into split_k CTAs each (their partial strips are summed in a fixed
+    // order by gather_tail_kernel), so that the tail costs 1/split_k of a wave instead of a whole one.
+    int item = blockIdx.x, slot = -1, ci_begin = 0, ci_end = p.Cin;
+    if (item >= p.full_items) {
+        slot = item - p.full_items;
+        const int part = slot % p.split_k;
+        item = p.full_items + slot / p.split_k;
+        ci_begin = (int)((long long)part * p.Cin / p.split_k);
+        ci_end = (int)((long long)(part + 1) * p.Cin / p.split_k);
+    }
+    const int tile_i = item % p.gx, cg = (item / p.gx) % p.gy;
+    const int np = item / (p.gx * p.gy);       // image pair
+    const int tyi = tile_i / p.tiles_x, txi = tile_i - tyi * p.tiles_x;
     const int x0 = txi * TW, y0 = tyi * TH;
-    const int np = blockIdx.z;                 // image pair
-    const int co0 = blockIdx.y * NW;
+    const int co0 = cg * NW;
     const int nrec = min(NW, p.Cout - co0) * p.G;
     const int nstage = p.nstage;
 
@@ -93,21 +171,8 @@ dau_gather_tma_kernel(const __grid_constant__ CUtensorMap in_map, const TGatherP
         for (int s = 0; s < nstage; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], NW); }
         fence_barrier_init();
     }
-    // mosaic maps of the tile's rows and columns for the store: (cell << 16 | pixel inside the
-    // cell), -1 for gap pixels -- the integer divisions happen once per CTA, not once per output
     __shared__ int s_rowmap[TH], s_colmap[TW];
-    if (tid < TH + TW) {
-        const bool row = tid < TH;
-        const int v = row ? y0 + tid : x0 + tid - TH;
-        const int ext = row ? p.H : p.W, pitch = row ? p.m.py : p.m.px, size = row ? p.m.H : p.m.W,
-                  cells = row ? p.m.ky : p.m.kx;
-        int code = -1;
-        if (v < ext) {
-            const int j = v / pitch, l = v - j * pitch;
-            if (l < size && j < cells) code = (j << 16) | l;
-        }
-        if (row) s_rowmap[tid] = code; else s_colmap[tid - TH] = code;
-    }
+    build_store_maps(p, x0, y0, tid, s_rowmap, s_colmap);
     __syncthreads();
 
     if (warp < 0) {
@@ -116,8 +181,8 @@ dau_gather_tma_kernel(const __grid_constant__ CUtensorMap in_map, const TGatherP
         if (warp == -4 && lane == 0) {
             if (!(p.debug & 1)) prefetch_map(&in_map);
             const uint32_t tx_bytes = ((p.debug & 2) ? 0 : GEO::TILE_BYTES) + ((p.debug & 4) ? 0 : nrec * (uint32_t)sizeof(UnitRec));
-            for (int ci = 0; ci < p.Cin; ++ci) {
-                const int st = ci % nstage, use = ci / nstage;
+            for (int ci = ci_begin; ci < ci_end; ++ci) {
+                const int st = (ci - ci_begin) % nstage, use = (ci - ci_begin) / nstage;
                 if (use > 0) mbar_wait(&empty_bar[st], (use - 1) & 1);
                 unsigned char* dst = smem_raw + (size_t)st * p.stage_bytes;
                 mbar_arrive_expect_tx(&full_bar[st], tx_bytes);
@@ -141,8 +206,8 @@ dau_gather_tma_kernel(const __grid_constant__ CUtensorMap in_map, const TGatherP
         for (int c = 0; c < C; ++c) acc[r][c] = make_float2(0.f, 0.f);
 
     const int lane_base = ly * R * ROW + lx;
-    for (int ci = 0; ci < p.Cin; ++ci) {
-        const int st = ci % nstage, use = ci / nstage;
+    for (int ci = ci_begin; ci < ci_end; ++ci) {
+        const int st = (ci - ci_begin) % nstage, use = (ci - ci_begin) / nstage;
         mbar_wait(&full_bar[st], use & 1);
         const unsigned char* sbase = smem_raw + (size_t)st * p.stage_bytes;
         if (co_valid) {
@@ -187,47 +252,47 @@ dau_gather_tma_kernel(const __grid_constant__ CUtensorMap in_map, const TGatherP
         if (lane == 0) mbar_arrive(&empty_bar[st]);
     }
 
-    // ---- epilogue: each image of the pair is stored once, float4 per row --------------------------
     if (!co_valid) return;
-    const float bv = p.bias ? __ldg(p.bias + co) : 0.f;
-    const int xs = x0 + lx * C;
-    const int H = p.H, W = p.W;
-    const bool ident = p.m.kx == 1 && p.m.ky == 1;
-    const int crop = p.crop, RH = p.m.H - 2 * crop, RW = p.m.W - 2 * crop;
-    const bool vec = ident && crop == 0 && ((W & 3) == 0) && (xs + C <= W);
-    const size_t rplane = (size_t)RH * RW;
+    if (slot >= 0) {
+        // part of a split item: the raw strip goes to the workspace, coalesced over the lanes
+        float2* dst = p.part + ((size_t)slot * NW + warp) * (R * C * 32) + lane;
 #pragma unroll
-    for (int img = 0; img < 2; ++img) {
-        const int n = 2 * np + img;
-        if (n >= p.N) break;
+        for (int r = 0; r < R; ++r)
 #pragma unroll
-        for (int r = 0; r < R; ++r) {
-            const int y = y0 + ly * R + r;
-            if (y >= H) continue;
-            float v[C];
+            for (int c = 0; c < C; ++c) dst[(r * C + c) * 32] = acc[r][c];
+        return;
+    }
+    store_strip(p, acc, np, co, lx, ly, x0, y0, s_rowmap, s_colmap);
+}
+
+// Sums the split_k partial strips of one tail item in part order and stores them like any other.
+__global__ void __launch_bounds__(NW * 32) gather_tail_kernel(const TGatherParams p) {
+    const int item = p.full_items + blockIdx.x;
+    const int tile_i = item % p.gx, cg = (item / p.gx) % p.gy, np = item / (p.gx * p.gy);
+    const int tyi = tile_i / p.tiles_x, txi = tile_i - tyi * p.tiles_x;
+    const int x0 = txi * TW, y0 = tyi * TH;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    __shared__ int s_rowmap[TH], s_colmap[TW];
+    build_store_maps(p, x0, y0, tid, s_rowmap, s_colmap);
+    __syncthreads();
+    const int co = cg * NW + warp;
+    if (co >= p.Cout) return;
+    float2 acc[R][C];
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+#pragma unroll
+        for (int c = 0; c < C; ++c) acc[r][c] = make_float2(0.f, 0.f);
+    for (int part = 0; part < p.split_k; ++part) {
+        const float2* src = p.part + ((size_t)(blockIdx.x * p.split_k + part) * NW + warp) * (R * C * 32) + lane;
+#pragma unroll
+        for (int r = 0; r < R; ++r)
 #pragma unroll
             for (int c = 0; c < C; ++c) {
-                v[c] = (img == 0 ? acc[r][c].x : acc[r][c].y) + bv;
-                if (p.relu) v[c] = fmaxf(v[c], 0.f);
+                const float2 v = src[(r * C + c) * 32];
+                acc[r][c].x += v.x; acc[r][c].y += v.y;
             }
-            if (vec) {
-                float* orow = p.out + ((size_t)n * p.Cout + co) * rplane + (size_t)y * W;
-                *reinterpret_cast<float4*>(orow + xs) = make_float4(v[0], v[1], v[2], v[3]);
-            } else {
-                // mosaic: gap pixels and cells beyond the batch are computed but never stored;
-                // crop: neither is the border of the same-size result
-                const int rm = s_rowmap[ly * R + r];
-#pragma unroll
-                for (int c = 0; c < C; ++c) {
-                    const int cm = s_colmap[lx * C + c];
-                    const int rn = (n * p.m.ky + (rm >> 16)) * p.m.kx + (cm >> 16);
-                    const int ry = (rm & 0xffff) - crop, rx = (cm & 0xffff) - crop;
-                    if ((rm | cm) >= 0 && rn < p.m.N && (unsigned)ry < (unsigned)RH && (unsigned)rx < (unsigned)RW)
-                        p.out[((size_t)rn * p.Cout + co) * rplane + (size_t)ry * RW + rx] = v[c];
-                }
-            }
-        }
     }
+    store_strip(p, acc, np, co, lane & (LX - 1), lane >> 4, x0, y0, s_rowmap, s_colmap);
 }
 
 constexpr int kHalos[4] = {4, 8, 16, 32};
@@ -240,8 +305,11 @@ void launch_t(const GatherPlan& plan, const CUtensorMap& map, const TGatherParam
                                             cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
         attr_set = true;
     }
-    dim3 grid(plan.grid_x, plan.grid_y, plan.grid_z);
-    dau_gather_tma_kernel<HALO><<<grid, NTHREADS, plan.smem_bytes, stream>>>(map, p);
+    const long long items = (long long)plan.grid_x * plan.grid_y * plan.grid_z;
+    const long long ctas = plan.full_items + (items - plan.full_items) * plan.split_k;
+    dau_gather_tma_kernel<HALO><<<(unsigned)ctas, NTHREADS, plan.smem_bytes, stream>>>(map, p);
+    if (plan.full_items < items)
+        gather_tail_kernel<<<(unsigned)(items - plan.full_items), NW * 32, 0, stream>>>(p);
 }
 
 template <int HALO>
@@ -259,7 +327,7 @@ size_t paired_layout_floats(int N, int Cn, int H, int W) {
     return (size_t)((N + 1) / 2) * Cn * H * 4 * qp * 2;
 }
 
-bool plan_gather_tma(int N, int Cin, int Cout, int G, int H, int W, int max_off, GatherPlan* out) {
+bool plan_gather_tma(int N, int Cin, int Cout, int G, int H, int W, int max_off, int num_sms, GatherPlan* out) {
     int hclass = 0;
     while (kHalos[hclass] < max_off) ++hclass;
     GatherPlan pl; memset(&pl, 0, sizeof(pl));
@@ -282,14 +350,33 @@ bool plan_gather_tma(int N, int Cin, int Cout, int G, int H, int W, int max_off,
     pl.grid_x = ((W + TW - 1) / TW) * ((H + TH - 1) / TH);
     pl.grid_y = (Cout + NW - 1) / NW;
     pl.grid_z = (N + 1) / 2;
-    if (pl.grid_y > 65535 || pl.grid_z > 65535) return false;
-    (void)Cin;
+    // One CTA per SM: `items` equal CTAs take ceil(items / SMs) rounds.  The items of the last,
+    // partial round are cut along the input channels into split_k CTAs whose partial strips are
+    // summed afterwards: the tail then costs ceil(tail * k / SMs) / k rounds instead of one.
+    const long long items = (long long)pl.grid_x * pl.grid_y * pl.grid_z;
+    if (items >= (1LL << 30)) return false;
+    const long long full = items / num_sms * num_sms, tail = items - full;
+    pl.full_items = (int)items; pl.split_k = 1;
+    pl.rounds = (double)((items + num_sms - 1) / num_sms);
+    if (tail > 0) {
+        int best_k = 1; double best_t = 1.0;
+        for (int k = 2; k <= 8 && Cin / k >= 4 && tail * k <= 512; ++k) {
+            const double t = (double)((tail * k + num_sms - 1) / num_sms) / k + 0.02;   // + the summing kernel
+            if (t < best_t - 1e-9) { best_t = t; best_k = k; }
+        }
+        if (best_k > 1) {
+            pl.full_items = (int)full; pl.split_k = best_k;
+            pl.rounds = (double)(full / num_sms) + best_t;
+        }
+    }
+    pl.part_bytes = (size_t)(items - pl.full_items) * pl.split_k * NW * R * C * 32 * sizeof(float2);
     *out = pl;
     return true;
 }
 
 void launch_gather_tma(const GatherPlan& plan, const float* in_paired, const UnitRec* table, const float* bias,
-                       float* out, const Mosaic& m, int Cin, int Cout, int G, cudaStream_t stream, int relu, int crop) {
+                       float* out, const Mosaic& m, int Cin, int Cout, int G, cudaStream_t stream, int relu, int crop,
+                       float* part_buf) {
     const int N = m.Nv, H = m.Hv, W = m.Wv;
     // tensor map of the paired gather layout: dims (q*2+i, p, y, plane)
     const uint64_t qv = (W + 3) / 4, qp = (qv + 1) / 2 * 2;
@@ -304,6 +391,9 @@ void launch_gather_tma(const GatherPlan& plan, const float* in_paired, const Uni
     p.tiles_x = (W + TW - 1) / TW; p.nstage = plan.nstage;
     p.stage_bytes = plan.stage_words * 4;
     p.m = m; p.relu = relu; p.crop = crop;
+    p.gx = plan.grid_x; p.gy = plan.grid_y; p.full_items = plan.full_items; p.split_k = plan.split_k;
+    p.part = reinterpret_cast<float2*>(part_buf);
+    DAU_CHECK(plan.part_bytes == 0 || part_buf != nullptr, 3, "gather plan splits its tail but no partial buffer was given");
     p.debug = getenv("DAU_DEBUG") ? atoi(getenv("DAU_DEBUG")) : 0;
     switch (plan.variant) {
         case 0: launch_t<4>(plan, map, p, stream); break;

@@ -94,10 +94,13 @@ const std::vector<int>& HostPipeline::schedule(int N, int S, int H, int W, int c
             const long long sms = l->num_sms();
             return (double)((ctas + sms - 1) / sms * sms) / (double)ctas;
         };
+        auto inv_eff_g = [&](const GatherPlan& g) {            // the gathers split their last wave
+            return g.rounds * l->num_sms() / ((double)g.grid_x * g.grid_y * g.grid_z);
+        };
         const GatherPlan& fp = l->fwd_plan(); const GatherPlan& bp = l->bwd_plan(); const GradPlan& gp = l->grad_plan();
         Slow v;
-        v.fwd = 0.24 * inv_eff((long long)fp.grid_x * fp.grid_y * fp.grid_z);
-        v.bwd = (want_dx ? 0.24 * inv_eff((long long)bp.grid_x * bp.grid_y * bp.grid_z) : 0.0) +
+        v.fwd = 0.24 * inv_eff_g(fp);
+        v.bwd = (want_dx ? 0.24 * inv_eff_g(bp) : 0.0) +
                 0.52 * inv_eff((long long)gp.grid_x * gp.grid_y * gp.grid_z);
         return slow[n] = v;
     };

@@ -79,7 +79,10 @@ struct GatherPlan {            // chosen once per shape by plan_gather_tma()
     int stage_words;           // words per pipeline stage (tile + unit records)
     int cout_per_cta;
     size_t smem_bytes;
-    int grid_x, grid_y, grid_z;
+    int grid_x, grid_y, grid_z;// items: tiles, groups of cout_per_cta output channels, image pairs
+    int full_items, split_k;   // items >= full_items (the last partial wave) run as split_k CTAs each
+    size_t part_bytes;         // workspace for their partial strips
+    double rounds;             // CTA rounds on this GPU (1 CTA per SM), for the host-step model
 };
 // out[n,co,y,x] = sum_{ci,g} gather(in[n,ci], table[ci][co][g]) (+ bias[co])
 
@@ -88,10 +91,10 @@ struct GatherPlan {            // chosen once per shape by plan_gather_tma()
 // (N, H, W below are the MOSAIC extents m.Nv, m.Hv, m.Wv; `in` / `out` of the producers and of
 // the gather's store are the caller's real NCHW tensors)
 size_t paired_layout_floats(int N, int Cn, int H, int W);
-bool plan_gather_tma(int N, int Cin, int Cout, int G, int H, int W, int max_off, GatherPlan* out);
+bool plan_gather_tma(int N, int Cin, int Cout, int G, int H, int W, int max_off, int num_sms, GatherPlan* out);
 void launch_gather_tma(const GatherPlan& p, const float* in_paired, const UnitRec* table, const float* bias,
                        float* out, const Mosaic& m, int Cin, int Cout, int G, cudaStream_t stream, int relu = 0,
-                       int crop = 0);
+                       int crop = 0, float* part_buf = nullptr);
 // Extras of the top-error blur (the prologue fused into the error load)
 struct ErrorSideArgs {
     const float* mask = nullptr;   // activation output, same shape as the error: error := 0 where mask <= 0

@@ -104,8 +104,8 @@ void DAUConvLayerB200::Reshape(int N, int S, int H, int W, size_t* fwd_ws, size_
     const int gap = std::max(max_off_, blur_kernel_size(sig) / 2);
     mosaic_ = plan_mosaic(N, H, W, gap);
     const Mosaic& m = mosaic_;
-    DAU_CHECK(plan_gather_tma(m.Nv, S, F_, G_, m.Hv, m.Wv, max_off_, &fwd_plan_), 4, "no forward gather plan for this shape");
-    DAU_CHECK(plan_gather_tma(m.Nv, F_, S, G_, m.Hv, m.Wv, max_off_, &bwd_plan_), 4, "no back-propagation gather plan for this shape");
+    DAU_CHECK(plan_gather_tma(m.Nv, S, F_, G_, m.Hv, m.Wv, max_off_, num_sms_, &fwd_plan_), 4, "no forward gather plan for this shape");
+    DAU_CHECK(plan_gather_tma(m.Nv, F_, S, G_, m.Hv, m.Wv, max_off_, num_sms_, &bwd_plan_), 4, "no back-propagation gather plan for this shape");
     DAU_CHECK(plan_grad_tma(m.Nv, S, F_, G_, m.Hv, m.Wv, max_off_, num_sms_, &grad_plan_), 4, "no gradient plan for this shape");
     // forward workspace: blurred input | unit table | flag
     size_t o = 0;
@@ -114,6 +114,7 @@ void DAUConvLayerB200::Reshape(int N, int S, int H, int W, size_t* fwd_ws, size_
     off_fwd_blur_ = o;  o = align_up(o + blur_in * sizeof(float));
     off_fwd_table_ = o; o = align_up(o + units * sizeof(UnitRec));
     off_fwd_flag_ = o;  o = align_up(o + 256);
+    off_fwd_part_ = o;  o = align_up(o + fwd_plan_.part_bytes);
     fwd_ws_ = o;
     // backward workspace: 4 derivative blurs | blurred error | two unit tables | split partials | flag
     o = 0;
@@ -126,6 +127,7 @@ void DAUConvLayerB200::Reshape(int N, int S, int H, int W, size_t* fwd_ws, size_
     off_bwd_gtable_ = o;  o = align_up(o + units * sizeof(UnitRec));
     off_bwd_partial_ = o; o = align_up(o + grad_plan_.partial_floats * sizeof(float));
     off_bwd_flag_ = o;    o = align_up(o + 256);
+    off_bwd_part_ = o;    o = align_up(o + bwd_plan_.part_bytes);
     bwd_ws_ = o;
     shaped_ = true;
     if (fwd_ws) *fwd_ws = fwd_ws_;
@@ -239,7 +241,8 @@ void DAUConvLayerB200::Forward_gpu(const float* bottom, float* w, float* mu1, fl
 
     tic(0, 3, stream);
     launch_gather_tma(fwd_plan_, xb, table, st_.bias_term ? bias : nullptr, top, mosaic_, S_, F_, G_, stream,
-                      activation_ == DAU_ACT_RELU ? 1 : 0, crop_);
+                      activation_ == DAU_ACT_RELU ? 1 : 0, crop_, reinterpret_cast<float*>(base + off_fwd_part_));
+    if (fwd_plan_.split_k > 1) ++launches_;           // the kernel that sums the split tail
     toc(0, 3, stream);
 }
 
@@ -321,7 +324,9 @@ void DAUConvLayerB200::Backward_gpu(const float* bottom, const float* top_error,
     if (want_input) {
         // gather with -mu and the parameters read transposed (base_dau_conv_layer.cu:290-325)
         tic(1, 5, stream);
-        launch_gather_tma(bwd_plan_, eb, btable, nullptr, bottom_error, mosaic_, F_, S_, G_, stream);
+        launch_gather_tma(bwd_plan_, eb, btable, nullptr, bottom_error, mosaic_, F_, S_, G_, stream, 0, 0,
+                          reinterpret_cast<float*>(base + off_bwd_part_));
+        if (bwd_plan_.split_k > 1) ++launches_;
         toc(1, 5, stream);
     }
     if ((flags & DAU_GRAD_BIAS) && st_.bias_term && dbias) {

@@ -75,7 +75,7 @@ private:
     Mosaic mosaic_{};          // how narrow images are packed for the TMA kernels (identity when wide)
     size_t fwd_ws_ = 0, bwd_ws_ = 0;
     // workspace carving (byte offsets)
-    size_t off_fwd_blur_ = 0, off_fwd_table_ = 0, off_fwd_flag_ = 0;
+    size_t off_fwd_blur_ = 0, off_fwd_table_ = 0, off_fwd_flag_ = 0, off_fwd_part_ = 0, off_bwd_part_ = 0;
     size_t off_bwd_xk_ = 0, off_bwd_esg_ = 0, off_bwd_eb_ = 0, off_bwd_table_ = 0, off_bwd_gtable_ = 0,
            off_bwd_partial_ = 0, off_bwd_flag_ = 0;
     int activation_ = 0;

@@ -259,7 +259,9 @@ def test_full_size_properties(cfg):
     k = torch.from_numpy(O.get_filters(0.5)[0].astype(np.float32)).to(dev)[None, None]
     ref = G * torch.nn.functional.conv2d(x.sum(1, keepdim=True), k, padding=3)
     assert float((y1[:, :1] - ref).abs().max()) <= 1e-4 * float(ref.abs().max())
-    assert float((y1 - y1[:, :1]).abs().max()) == 0.0     # every feature saw the same units
+    # every feature saw the same units; features of the gather's split tail wave add their input
+    # channels in split_k partial sums, so equality holds to fp32 rounding, not bit for bit
+    assert float((y1 - y1[:, :1]).abs().max()) <= 1e-5 * float(ref.abs().max())
 
 
 # ---- row f3: bias + ReLU fused into the forward store, ReLU mask fused into every error load ------
