@@ -43,14 +43,17 @@ namespace {
 
 using namespace tma;
 
-constexpr int R = 16, C = 4, LX = 16, LY = 2, NW = 8;
+// lane = (lx 0..15, ly 0..1) owns an R x 4 strip of both images; R (16, 15 or 14) is picked per shape so
+// that the 2R-row tiles waste the fewest rows (28-row maps: R = 14, the 30-row mosaic of 13 x 13 maps: R = 15)
+constexpr int C = 4, LX = 16, LY = 2, NW = 8;
 // CTA = 3 warpgroups: warpgroup 0 holds the producer lane and gives its registers away
 // (setmaxnreg.dec), warpgroups 1-2 are the 8 consumer warps and grow to CONS_REGS each.
 constexpr int NTHREADS = (NW + 4) * 32, PROD_REGS = 40, CONS_REGS = 232;
-constexpr int TW = LX * C, TH = LY * R;
+constexpr int TW = LX * C;
 
-template <int HALO>
+template <int HALO, int R>
 struct TGeom {
+    static constexpr int TH = LY * R;
     // the innermost TMA start coordinate must be 16-byte aligned: 2*(x0-HX)/4 floats -> HX % 8 == 0
     static constexpr int HX = (HALO + 7) / 8 * 8, HY = HALO;
     static constexpr int QS = (TW + 2 * HX) / 4;          // float2 per column plane
@@ -75,6 +78,7 @@ struct TGatherParams {
 
 // Mosaic maps of a tile's rows and columns for the store: (cell << 16 | pixel inside the cell), -1
 // for gap pixels -- the integer divisions happen once per CTA, not once per output.
+template <int TH>
 __device__ __forceinline__ void build_store_maps(const TGatherParams& p, int x0, int y0, int tid, int* s_rowmap,
                                                  int* s_colmap) {
     if (tid < TH + TW) {
@@ -93,6 +97,7 @@ __device__ __forceinline__ void build_store_maps(const TGatherParams& p, int x0,
 
 // Epilogue: bias, activation, and the store of a lane's 16 x 4 strip of both images of the pair
 // into the caller's NCHW tensor (float4 per row when the planes allow it).
+template <int R>
 __device__ __forceinline__ void store_strip(const TGatherParams& p, const float2 (&acc)[R][C], int np, int co, int lx,
                                             int ly, int x0, int y0, const int* s_rowmap, const int* s_colmap) {
     const float bv = p.bias ? __ldg(p.bias + co) : 0.f;
@@ -136,10 +141,11 @@ __device__ __forceinline__ void store_strip(const TGatherParams& p, const float2
     }
 }
 
-template <int HALO>
+template <int HALO, int R>
 __global__ void __launch_bounds__(NTHREADS, 1)
 dau_gather_tma_kernel(const __grid_constant__ CUtensorMap in_map, const TGatherParams p) {
-    using GEO = TGeom<HALO>;
+    using GEO = TGeom<HALO, R>;
+    constexpr int TH = GEO::TH;
     constexpr int QS = GEO::QS, ROW = GEO::ROW;
     extern __shared__ unsigned char smem_dyn[];
     __shared__ uint64_t full_bar[8], empty_bar[8];
@@ -172,7 +178,7 @@ dau_gather_tma_kernel(const __grid_constant__ CUtensorMap in_map, const TGatherP
         fence_barrier_init();
     }
     __shared__ int s_rowmap[TH], s_colmap[TW];
-    build_store_maps(p, x0, y0, tid, s_rowmap, s_colmap);
+    build_store_maps<TH>(p, x0, y0, tid, s_rowmap, s_colmap);
     __syncthreads();
 
     if (warp < 0) {
@@ -262,18 +268,20 @@ dau_gather_tma_kernel(const __grid_constant__ CUtensorMap in_map, const TGatherP
             for (int c = 0; c < C; ++c) dst[(r * C + c) * 32] = acc[r][c];
         return;
     }
-    store_strip(p, acc, np, co, lx, ly, x0, y0, s_rowmap, s_colmap);
+    store_strip<R>(p, acc, np, co, lx, ly, x0, y0, s_rowmap, s_colmap);
 }
 
 // Sums the split_k partial strips of one tail item in part order and stores them like any other.
+template <int R>
 __global__ void __launch_bounds__(NW * 32) gather_tail_kernel(const TGatherParams p) {
+    constexpr int TH = LY * R;
     const int item = p.full_items + blockIdx.x;
     const int tile_i = item % p.gx, cg = (item / p.gx) % p.gy, np = item / (p.gx * p.gy);
     const int tyi = tile_i / p.tiles_x, txi = tile_i - tyi * p.tiles_x;
     const int x0 = txi * TW, y0 = tyi * TH;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     __shared__ int s_rowmap[TH], s_colmap[TW];
-    build_store_maps(p, x0, y0, tid, s_rowmap, s_colmap);
+    build_store_maps<TH>(p, x0, y0, tid, s_rowmap, s_colmap);
     __syncthreads();
     const int co = cg * NW + warp;
     if (co >= p.Cout) return;
@@ -292,29 +300,29 @@ __global__ void __launch_bounds__(NW * 32) gather_tail_kernel(const TGatherParam
                 acc[r][c].x += v.x; acc[r][c].y += v.y;
             }
     }
-    store_strip(p, acc, np, co, lane & (LX - 1), lane >> 4, x0, y0, s_rowmap, s_colmap);
+    store_strip<R>(p, acc, np, co, lane & (LX - 1), lane >> 4, x0, y0, s_rowmap, s_colmap);
 }
 
 constexpr int kHalos[4] = {4, 8, 16, 32};
 
-template <int HALO>
+template <int HALO, int R>
 void launch_t(const GatherPlan& plan, const CUtensorMap& map, const TGatherParams& p, cudaStream_t stream) {
     static bool attr_set = false;
     if (!attr_set) {
-        DAU_CUDA_CHECK(cudaFuncSetAttribute(dau_gather_tma_kernel<HALO>,
+        DAU_CUDA_CHECK(cudaFuncSetAttribute(dau_gather_tma_kernel<HALO, R>,
                                             cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
         attr_set = true;
     }
     const long long items = (long long)plan.grid_x * plan.grid_y * plan.grid_z;
     const long long ctas = plan.full_items + (items - plan.full_items) * plan.split_k;
-    dau_gather_tma_kernel<HALO><<<(unsigned)ctas, NTHREADS, plan.smem_bytes, stream>>>(map, p);
+    dau_gather_tma_kernel<HALO, R><<<(unsigned)ctas, NTHREADS, plan.smem_bytes, stream>>>(map, p);
     if (plan.full_items < items)
-        gather_tail_kernel<<<(unsigned)(items - plan.full_items), NW * 32, 0, stream>>>(p);
+        gather_tail_kernel<R><<<(unsigned)(items - plan.full_items), NW * 32, 0, stream>>>(p);
 }
 
-template <int HALO>
+template <int HALO, int R>
 void fill_t(GatherPlan& pl) {
-    using GEO = TGeom<HALO>;
+    using GEO = TGeom<HALO, R>;
     pl.halo_x = GEO::HX; pl.halo_y = GEO::HY;
     pl.row_stride = GEO::ROW * 2; pl.img_stride = 0;
     pl.stage_words = GEO::TILE_BYTES / 4;
@@ -332,13 +340,30 @@ bool plan_gather_tma(int N, int Cin, int Cout, int G, int H, int W, int max_off,
     while (kHalos[hclass] < max_off) ++hclass;
     GatherPlan pl; memset(&pl, 0, sizeof(pl));
     pl.kind = 1; pl.variant = hclass;
-    pl.tile_w = TW; pl.tile_h = TH; pl.imgs = 2; pl.cout_per_cta = NW;
-    switch (hclass) {
-        case 0: fill_t<4>(pl); break;
-        case 1: fill_t<8>(pl); break;
-        case 2: fill_t<16>(pl); break;
-        default: fill_t<32>(pl); break;
+    // strip rows R: the 2R-row tiling that computes the fewest rows (ties: the taller strip)
+    int R = 16;
+    {
+        long best = -1;
+        for (int r : {16, 15, 14}) {
+            const long rows = (long)((H + 2 * r - 1) / (2 * r)) * 2 * r;
+            if (best < 0 || rows < best) { best = rows; R = r; }
+        }
     }
+    const int TH = LY * R;
+    pl.tile_w = TW; pl.tile_h = TH; pl.imgs = 2; pl.cout_per_cta = NW;
+#define DAU_FILL(HALO)                                              \
+    switch (R) {                                                    \
+        case 16: fill_t<HALO, 16>(pl); break;                       \
+        case 15: fill_t<HALO, 15>(pl); break;                       \
+        default: fill_t<HALO, 14>(pl); break;                       \
+    }
+    switch (hclass) {
+        case 0: DAU_FILL(4); break;
+        case 1: DAU_FILL(8); break;
+        case 2: DAU_FILL(16); break;
+        default: DAU_FILL(32); break;
+    }
+#undef DAU_FILL
     const size_t tile_bytes = (size_t)pl.stage_words * 4;
     const size_t stage = (tile_bytes + (size_t)NW * G * sizeof(UnitRec) + 127) / 128 * 128;
     int nstage = (int)((200 * 1024 - 128) / stage);
@@ -383,6 +408,7 @@ void launch_gather_tma(const GatherPlan& plan, const float* in_paired, const Uni
     const uint64_t dims[4] = {2 * qv, 4, (uint64_t)H, (uint64_t)((N + 1) / 2) * Cin};
     const uint64_t strides[3] = {qp * 8, 4 * qp * 8, (uint64_t)H * 4 * qp * 8};
     const int halo_q2 = 2 * ((TW + 2 * plan.halo_x) / 4);
+    const int TH = plan.tile_h;
     const uint32_t box[4] = {(uint32_t)halo_q2, 4, (uint32_t)(TH + 2 * plan.halo_y), 1};
     const CUtensorMap map = make_map_f32(in_paired, 4, dims, strides, box);
     TGatherParams p;
@@ -395,12 +421,19 @@ void launch_gather_tma(const GatherPlan& plan, const float* in_paired, const Uni
     p.part = reinterpret_cast<float2*>(part_buf);
     DAU_CHECK(plan.part_bytes == 0 || part_buf != nullptr, 3, "gather plan splits its tail but no partial buffer was given");
     p.debug = getenv("DAU_DEBUG") ? atoi(getenv("DAU_DEBUG")) : 0;
-    switch (plan.variant) {
-        case 0: launch_t<4>(plan, map, p, stream); break;
-        case 1: launch_t<8>(plan, map, p, stream); break;
-        case 2: launch_t<16>(plan, map, p, stream); break;
-        default: launch_t<32>(plan, map, p, stream); break;
+#define DAU_LAUNCH(HALO)                                                     \
+    switch (plan.tile_h / LY) {                                              \
+        case 16: launch_t<HALO, 16>(plan, map, p, stream); break;            \
+        case 15: launch_t<HALO, 15>(plan, map, p, stream); break;            \
+        default: launch_t<HALO, 14>(plan, map, p, stream); break;            \
     }
+    switch (plan.variant) {
+        case 0: DAU_LAUNCH(4); break;
+        case 1: DAU_LAUNCH(8); break;
+        case 2: DAU_LAUNCH(16); break;
+        default: DAU_LAUNCH(32); break;
+    }
+#undef DAU_LAUNCH
     DAU_CUDA_CHECK(cudaGetLastError());
 }
 

@@ -28,7 +28,7 @@ bool edge_rule(int n) {
 
 }  // namespace
 
-// Packs narrow images kx x ky to mosaic images so that the 64 x 16 tiles of the TMA kernels are
+// Packs narrow images kx x ky to mosaic images so that the 64-pixel-wide tiles of the TMA kernels are
 // mostly image and not padding; scores every (kx, ky) by the fraction of computed pixels that
 // are real ones (tiles are 64 wide; 32 rows for the gathers, 4 for the gradients) and by how
 // evenly the batch divides into pairs of mosaics.
@@ -45,9 +45,11 @@ Mosaic plan_mosaic(int N, int H, int W, int gap) {
             if (cells > 1 && 2 * cells > N) continue;          // never pad the batch by more than a pair
             const int Nv = (N + cells - 1) / cells, pairs = (Nv + 1) / 2;
             const double ex = (double)kx * W / (64.0 * ((Wv + 63) / 64));
-            // half of the flops run on 32-row tiles (gathers), half on 4-row tiles (gradients)
-            const double ey = 0.5 * (double)ky * H / (32.0 * ((Hv + 31) / 32)) +
-                              0.5 * (double)ky * H / (4.0 * ((Hv + 3) / 4));
+            // half of the flops run on the gathers' tiles (32, 30 or 28 rows, whichever wastes the
+            // fewest: plan_gather_tma), half on 4-row tiles (gradients)
+            int grows = 1 << 30;
+            for (int th : {32, 30, 28}) grows = std::min(grows, (Hv + th - 1) / th * th);
+            const double ey = 0.5 * (double)ky * H / grows + 0.5 * (double)ky * H / (4.0 * ((Hv + 3) / 4));
             const double eb = (double)N / ((double)pairs * 2 * cells);
             const double score = ex * ey * eb - 1e-3 * cells;
             if (score > best_score + 1e-12) {
