@@ -33,6 +33,7 @@ struct UnitPrepArgs {
     int ghalo_x, ghalo_y;    // halo of the gradient table (its kernel may round differently)
     int max_off;             // kernel_size/2: integer offsets are clamped to [-max_off, max_off-1]
     int use_interpolation;
+    float mu_center = 0.f;   // kernel_size/2 when offsets_already_centered == 0, else 0
 };
 
 void launch_unit_prep(const UnitPrepArgs& a, UnitRec* fwd, UnitRec* bwd, UnitRec* grad,

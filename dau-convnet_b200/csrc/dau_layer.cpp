@@ -79,7 +79,6 @@ DAUConvLayerB200::DAUConvLayerB200(const dau_settings_t& s, int device) : st_(s)
     // (height_out_ = H + 2*pad - ks + 1, base_dau_conv_layer.cpp:20-22; border = H/2 - H_out/2, :544-545)
     crop_ = (s.kernel_size - 1) / 2 - s.pad;
     DAU_CHECK(s.pad >= 0 && crop_ >= 0, 4, "pad must be in [0, (kernel_size-1)/2] (output never larger than the input)");
-    DAU_CHECK(s.offsets_already_centered != 0, 4, "only centred offsets are supported");
     G_ = s.number_units_x * s.number_units_y;
     DAU_CHECK(s.number_units_ignore >= 0 && s.number_units_ignore < G_ + 1, 1, "number_units_ignore out of range");
     F_ = s.num_output;
@@ -221,8 +220,9 @@ void DAUConvLayerB200::Forward_gpu(const float* bottom, float* w, float* mu1, fl
 
     if (st_.unit_bounds_guard) {                      // base_dau_conv_layer.cu:33-49
         tic(0, 0, stream);
-        const float lim = (float)max_off_ - st_.component_border_bound;
-        launch_clip_params(mu1, mu2, sigma, units, -lim, lim, st_.sigma_lower_bound, stream);
+        // centred offsets live in [-ks/2 + bound, ks/2 - bound], corner-based ones in [bound, ks-1-bound]
+        const float lim = (float)max_off_ - st_.component_border_bound, c = mu_center();
+        launch_clip_params(mu1, mu2, sigma, units, c - lim, c + lim, st_.sigma_lower_bound, stream);
         toc(0, 0, stream);
     }
     const BlurFactors& f = factors_for(sigma, stream);
@@ -237,7 +237,7 @@ void DAUConvLayerB200::Forward_gpu(const float* bottom, float* w, float* mu1, fl
     ua.g_active = G_ - st_.number_units_ignore;
     ua.halo_x = fwd_plan_.halo_x; ua.halo_y = fwd_plan_.halo_y; ua.max_off = max_off_;
     ua.ghalo_x = ua.halo_x; ua.ghalo_y = ua.halo_y;
-    ua.use_interpolation = st_.use_interpolation;
+    ua.use_interpolation = st_.use_interpolation; ua.mu_center = mu_center();
     launch_unit_prep(ua, table, nullptr, nullptr, flag, stream);
     toc(0, 2, stream);
 
@@ -279,7 +279,7 @@ void DAUConvLayerB200::Backward_gpu(const float* bottom, const float* top_error,
     UnitPrepArgs ua;
     ua.w = w; ua.mu1 = mu1; ua.mu2 = mu2; ua.S = S_; ua.G = G_; ua.F = F_;
     ua.g_active = G_ - st_.number_units_ignore;
-    ua.max_off = max_off_; ua.use_interpolation = st_.use_interpolation;
+    ua.max_off = max_off_; ua.use_interpolation = st_.use_interpolation; ua.mu_center = mu_center();
 
     if (want_params) {
         tic(1, 0, stream);

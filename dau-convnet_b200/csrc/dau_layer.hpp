@@ -63,6 +63,8 @@ public:
 
 private:
     const BlurFactors& factors_for(const float* sigma_dev, cudaStream_t stream);
+    // offsets_already_centered == 0: mu counts from the kernel's corner (the Caffe layer's convention)
+    float mu_center() const { return st_.offsets_already_centered ? 0.f : (float)(st_.kernel_size / 2); }
     void tic(int which, int idx, cudaStream_t s);
     void toc(int which, int idx, cudaStream_t s);
 

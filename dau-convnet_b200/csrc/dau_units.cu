@@ -28,7 +28,8 @@ __global__ void unit_prep_kernel(UnitPrepArgs a, UnitRec* __restrict__ fwd, Unit
     const int total = a.S * a.G * a.F;
     if (i >= total) return;
     const int f = i % a.F, g = (i / a.F) % a.G, s = i / (a.F * a.G);
-    float w = a.w[i], m1 = a.mu1[i], m2 = a.mu2[i];
+    // offsets counted from the kernel's corner become offsets from its centre (base_dau_conv_layer.cpp:574-575)
+    float w = a.w[i], m1 = a.mu1[i] - a.mu_center, m2 = a.mu2[i] - a.mu_center;
     if (isnan(m1) || isnan(m2)) {           // reference: FAILED_PRECONDITION (dau_conv_op.cpp:258-262)
         if (nan_flag) atomicExch(nan_flag, 1);
         m1 = 0.f; m2 = 0.f; w = 0.f;

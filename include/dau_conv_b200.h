@@ -62,7 +62,7 @@ typedef struct dau_settings_t {
     int32_t forbid_positive_dim1;
     int32_t ignore_edge_gradients; /* TF attr unit_testing */
     int32_t unit_bounds_guard;     /* clip mu/sigma IN PLACE before use (Forward_gpu :33-49) */
-    int32_t offsets_already_centered; /* must be 1 */
+    int32_t offsets_already_centered; /* default 1 (TF op); 0: mu counts from the kernel corner, centre = mu - kernel_size/2 (Caffe layer, base_dau_conv_layer.cpp:574-575) */
     int32_t learn_sigma;           /* 0 => sigma gradient skipped (last_k_optional) */
     float   component_border_bound;
     float   sigma_lower_bound;

@@ -430,3 +430,36 @@ def test_random_shapes_and_flags(case):
                              ignore_edge_gradients=a["unit_testing"], **kw)
     for name, got, want in zip(["dx", "dw", "dmu1", "dmu2", "dsigma"], g, ref):
         close(got, want, name, scale_atol=name != "dx")
+
+
+def test_corner_based_offsets_equal_centred_ones():
+    """offsets_already_centered = 0 (the Caffe layer's convention): mu counts from the kernel's corner and
+    the layer subtracts kernel_size/2 (base_dau_conv_layer.cpp:574-575, :817-818; rot(mu) = ks-1-mu for
+    the back-propagation, base_dau_conv_layer.cu:302-314); the guard then clips to [bound, ks-1-bound]
+    (:38-42).  Same numbers as the centred layer on mu - ks/2, bit for bit."""
+    import torch
+    import dau_conv
+    from dau_conv import _lib
+    x, err, w, mu1, mu2, ks = _case((4, 24, 19, 3, 5, (1, 2), 9, 3.9), 21)
+    mu1, mu2 = np.round(mu1 * 1024) / 1024, np.round(mu2 * 1024) / 1024     # mu + ks/2 is then exact in fp32
+    mu1, mu2 = mu1.astype(np.float32), mu2.astype(np.float32)
+    dev = torch.device("cuda:0")
+    sig = np.full(w.shape, 0.5, np.float32)
+    res = []
+    for centred in (1, 0):
+        st = _lib.default_settings(num_output=5, number_units_x=1, number_units_y=2, kernel_size=ks, pad=4,
+                                   offsets_already_centered=centred, unit_bounds_guard=1 - centred,
+                                   component_border_bound=0.01, sigma_lower_bound=0.3)
+        h = dau_conv.DAULayerHandle(st, dev)
+        h.set_sigma_hint(0.5)
+        shift = 0.0 if centred else float(ks // 2)
+        t = [torch.from_numpy(np.ascontiguousarray(a)).to(dev) for a in (x, w, mu1 + shift, mu2 + shift, sig)]
+        y = h.forward(*t)
+        g = h.backward(t[0], torch.from_numpy(err).to(dev), *t[1:])
+        torch.cuda.synchronize()
+        if not centred:          # all offsets were inside [0.01, ks-1-0.01]: the guard left them alone
+            assert np.array_equal(t[2].cpu().numpy(), (mu1 + shift).astype(np.float32))
+        res.append([y.cpu().numpy()] + [v.cpu().numpy() for v in g])
+    for a, b in zip(*res):
+        assert np.array_equal(a, b)
+    close(res[1][0], O.forward(x, w, mu1, mu2, [0.5]), "y")
