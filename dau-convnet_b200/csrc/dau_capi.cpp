@@ -135,6 +135,11 @@ dau_status_t dau_get_output_size(dau_handle_t* h, int* h_out, int* w_out) {
     });
 }
 
+dau_status_t dau_take_nan_flag(dau_handle_t* h, int* found, void* stream) {
+    if (!h || !found) return fail(DAU_ERR_INVALID_ARGUMENT, "dau_take_nan_flag: NULL argument");
+    return guarded([&] { *found = h->layer->take_nan_flag((cudaStream_t)stream) ? 1 : 0; });
+}
+
 dau_status_t dau_set_activation(dau_handle_t* h, int activation) {
     if (!h) return fail(DAU_ERR_INVALID_ARGUMENT, "dau_set_activation: NULL handle");
     return guarded([&] { h->layer->set_activation(activation); });

@@ -88,9 +88,22 @@ DAUConvLayerB200::DAUConvLayerB200(const dau_settings_t& s, int device) : st_(s)
     DAU_CUDA_CHECK(cudaGetDeviceProperties(&prop, device));
     DAU_CHECK(prop.major >= 10, 4, "this library is built for sm_100a (B200) only");
     num_sms_ = prop.multiProcessorCount;
+    // sticky "a mu was NaN" flag, read and cleared by take_nan_flag()
+    DAU_CUDA_CHECK(cudaMalloc(&nan_flag_, sizeof(int)));
+    DAU_CUDA_CHECK(cudaMemset(nan_flag_, 0, sizeof(int)));
+}
+
+bool DAUConvLayerB200::take_nan_flag(cudaStream_t stream) {
+    int v = 0;
+    DAU_CUDA_CHECK(cudaSetDevice(device_));
+    DAU_CUDA_CHECK(cudaMemcpyAsync(&v, nan_flag_, sizeof(int), cudaMemcpyDeviceToHost, stream));
+    DAU_CUDA_CHECK(cudaMemsetAsync(nan_flag_, 0, sizeof(int), stream));
+    DAU_CUDA_CHECK(cudaStreamSynchronize(stream));
+    return v != 0;
 }
 
 DAUConvLayerB200::~DAUConvLayerB200() {
+    if (nan_flag_) cudaFree(nan_flag_);
     for (int w = 0; w < 2; ++w)
         for (auto& sl : slots_[w]) { cudaEventDestroy(sl.beg); cudaEventDestroy(sl.end); }
 }
@@ -108,16 +121,15 @@ void DAUConvLayerB200::Reshape(int N, int S, int H, int W, size_t* fwd_ws, size_
     DAU_CHECK(plan_gather_tma(m.Nv, S, F_, G_, m.Hv, m.Wv, max_off_, num_sms_, &fwd_plan_), 4, "no forward gather plan for this shape");
     DAU_CHECK(plan_gather_tma(m.Nv, F_, S, G_, m.Hv, m.Wv, max_off_, num_sms_, &bwd_plan_), 4, "no back-propagation gather plan for this shape");
     DAU_CHECK(plan_grad_tma(m.Nv, S, F_, G_, m.Hv, m.Wv, max_off_, num_sms_, &grad_plan_), 4, "no gradient plan for this shape");
-    // forward workspace: blurred input | unit table | flag
+    // forward workspace: blurred input | unit table | partial strips of the gather's split tail
     size_t o = 0;
     const size_t blur_in = paired_layout_floats(m.Nv, S, m.Hv, m.Wv);
     const size_t blur_out = paired_layout_floats(m.Nv, F_, m.Hv, m.Wv);
     off_fwd_blur_ = o;  o = align_up(o + blur_in * sizeof(float));
     off_fwd_table_ = o; o = align_up(o + units * sizeof(UnitRec));
-    off_fwd_flag_ = o;  o = align_up(o + 256);
     off_fwd_part_ = o;  o = align_up(o + fwd_plan_.part_bytes);
     fwd_ws_ = o;
-    // backward workspace: 4 derivative blurs | blurred error | two unit tables | split partials | flag
+    // backward workspace: 4 derivative blurs | blurred error | two unit tables | split partials | gather tail strips
     o = 0;
     const size_t xk_floats = strip_layout_floats(m.Nv, S, m.Hv, m.Wv);
     const size_t esg_floats = error_layout_floats(m.Nv, F_, m.Hv, m.Wv);
@@ -127,7 +139,6 @@ void DAUConvLayerB200::Reshape(int N, int S, int H, int W, size_t* fwd_ws, size_
     off_bwd_table_ = o;   o = align_up(o + units * sizeof(UnitRec));
     off_bwd_gtable_ = o;  o = align_up(o + units * sizeof(UnitRec));
     off_bwd_partial_ = o; o = align_up(o + grad_plan_.partial_floats * sizeof(float));
-    off_bwd_flag_ = o;    o = align_up(o + 256);
     off_bwd_part_ = o;    o = align_up(o + bwd_plan_.part_bytes);
     bwd_ws_ = o;
     shaped_ = true;
@@ -215,7 +226,6 @@ void DAUConvLayerB200::Forward_gpu(const float* bottom, float* w, float* mu1, fl
     char* base = static_cast<char*>(ws);
     float* xb = reinterpret_cast<float*>(base + off_fwd_blur_);
     UnitRec* table = reinterpret_cast<UnitRec*>(base + off_fwd_table_);
-    int* flag = reinterpret_cast<int*>(base + off_fwd_flag_);
     const int units = S_ * G_ * F_;
 
     if (st_.unit_bounds_guard) {                      // base_dau_conv_layer.cu:33-49
@@ -238,7 +248,7 @@ void DAUConvLayerB200::Forward_gpu(const float* bottom, float* w, float* mu1, fl
     ua.halo_x = fwd_plan_.halo_x; ua.halo_y = fwd_plan_.halo_y; ua.max_off = max_off_;
     ua.ghalo_x = ua.halo_x; ua.ghalo_y = ua.halo_y;
     ua.use_interpolation = st_.use_interpolation; ua.mu_center = mu_center();
-    launch_unit_prep(ua, table, nullptr, nullptr, flag, stream);
+    launch_unit_prep(ua, table, nullptr, nullptr, nan_flag_, stream);
     toc(0, 2, stream);
 
     tic(0, 3, stream);
@@ -269,7 +279,6 @@ void DAUConvLayerB200::Backward_gpu(const float* bottom, const float* top_error,
     UnitRec* btable = reinterpret_cast<UnitRec*>(base + off_bwd_table_);
     UnitRec* gtable = reinterpret_cast<UnitRec*>(base + off_bwd_gtable_);
     float* partial = reinterpret_cast<float*>(base + off_bwd_partial_);
-    int* flag = reinterpret_cast<int*>(base + off_bwd_flag_);
     const BlurFactors& f = factors_for(sigma, stream);
 
     const bool want_params = (flags & (DAU_GRAD_W | DAU_GRAD_MU1 | DAU_GRAD_MU2 | DAU_GRAD_SIGMA)) != 0;
@@ -291,7 +300,7 @@ void DAUConvLayerB200::Backward_gpu(const float* bottom, const float* top_error,
         tic(1, 1, stream);
         ua.halo_x = bwd_plan_.halo_x; ua.halo_y = bwd_plan_.halo_y;
         ua.ghalo_x = grad_plan_.halo_x; ua.ghalo_y = grad_plan_.halo_y;
-        launch_unit_prep(ua, nullptr, want_input ? btable : nullptr, want_params ? gtable : nullptr, flag, stream);
+        launch_unit_prep(ua, nullptr, want_input ? btable : nullptr, want_params ? gtable : nullptr, nan_flag_, stream);
         toc(1, 1, stream);
     }
     const int mrow = st_.ignore_edge_gradients && edge_rule(H_out()) ? 1 : 0;

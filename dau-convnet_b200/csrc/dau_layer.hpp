@@ -44,6 +44,10 @@ public:
     // reference reads it once in LayerSetUp, base_dau_conv_layer.hpp:266-275).  Reshape sizes the
     // mosaic gap from it, so set it BEFORE Reshape when sigma is larger than the op default 0.5.
     void set_sigma_hint(float v) { sigma_hint_ = v; }
+    // true if any mu was NaN in a forward / backward call since the last query (such units are
+    // treated as w = 0); blocks on `stream`.  The TF op fails the call instead (dau_conv_op.cpp:258-262)
+    // because it reads max|mu| back on every call anyway; here the read is the caller's choice.
+    bool take_nan_flag(cudaStream_t stream);
     void enable_timing(bool e);
     int  get_timing(int which, float* ms, int cap);
     static const char* timing_name(int which, int idx);
@@ -77,10 +81,11 @@ private:
     Mosaic mosaic_{};          // how narrow images are packed for the TMA kernels (identity when wide)
     size_t fwd_ws_ = 0, bwd_ws_ = 0;
     // workspace carving (byte offsets)
-    size_t off_fwd_blur_ = 0, off_fwd_table_ = 0, off_fwd_flag_ = 0, off_fwd_part_ = 0, off_bwd_part_ = 0;
+    size_t off_fwd_blur_ = 0, off_fwd_table_ = 0, off_fwd_part_ = 0, off_bwd_part_ = 0;
     size_t off_bwd_xk_ = 0, off_bwd_esg_ = 0, off_bwd_eb_ = 0, off_bwd_table_ = 0, off_bwd_gtable_ = 0,
-           off_bwd_partial_ = 0, off_bwd_flag_ = 0;
+           off_bwd_partial_ = 0;
     int activation_ = 0;
+    int* nan_flag_ = nullptr;  // device int, owned
     int crop_ = 0;             // (kernel_size-1)/2 - pad
     float sigma_hint_ = 0.f;
     float cached_sigma_ = -1.f;

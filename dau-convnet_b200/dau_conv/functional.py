@@ -117,6 +117,14 @@ class DAULayerHandle(object):
         return int(_lib.lib.dau_launch_count(self._h))
 
     # -- the two calls of the contract ---------------------------------------------------------
+    def take_nan_flag(self):
+        """True if a mu was NaN in any call since the last query (the TF op raises instead,
+        dau_conv_op.cpp:258-262); blocks on the current stream."""
+        found = C.c_int(0)
+        _lib.check(_lib.lib.dau_take_nan_flag(self._h, C.byref(found),
+                                              torch.cuda.current_stream(self.device).cuda_stream))
+        return bool(found.value)
+
     def set_activation(self, activation):
         """dau_set_activation: DAU_ACT_NONE (0) or DAU_ACT_RELU (1), fused into forward / backward."""
         _lib.check(_lib.lib.dau_set_activation(self._h, int(activation)))
@@ -217,13 +225,17 @@ def _sigma_of(sigma, sigma_value):
     return float(sigma.reshape(-1)[0]) if sigma_value is None else float(sigma_value)
 
 
-def dau_conv_op(input, weights, mu1, mu2, sigma, sigma_value=None, **attrs):
-    """TF op DAUConv: output[N,F,H,W] (forward only, no autograd)."""
+def dau_conv_op(input, weights, mu1, mu2, sigma, sigma_value=None, check_nan=False, **attrs):
+    """TF op DAUConv: output[N,F,H,W] (forward only, no autograd).  check_nan=True reproduces the op's
+    FAILED_PRECONDITION on NaN offsets (dau_conv_op.cpp:258-262) at the price of one host sync."""
     _check_inputs(input, weights, mu1, mu2, sigma, attrs)
     h = get_handle(input.device, **attrs)
     h.set_sigma_hint(_sigma_of(sigma, sigma_value))
-    return h.forward(input.contiguous(), weights.contiguous(), mu1.contiguous(), mu2.contiguous(),
-                     sigma.contiguous())
+    out = h.forward(input.contiguous(), weights.contiguous(), mu1.contiguous(), mu2.contiguous(),
+                    sigma.contiguous())
+    if check_nan and h.take_nan_flag():
+        raise RuntimeError("DAUConv: mu1 or mu2 contains NaN values")
+    return out
 
 
 def dau_conv_grad_op(grad, input, weights, mu1, mu2, sigma, sigma_value=None, **attrs):

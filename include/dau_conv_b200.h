@@ -119,6 +119,12 @@ dau_status_t dau_backward(dau_handle_t* h, const float* bottom_dev, const float*
                           float* dbias_dev, unsigned flags,
                           void* workspace_dev, size_t workspace_bytes, void* stream);
 
+/* *found = 1 if any mu1 / mu2 was NaN in a dau_forward / dau_backward call on this handle since the
+ * last query (such units contribute nothing), then clears the flag.  Blocks on `stream`.  The TF op
+ * fails such a call with FAILED_PRECONDITION (dau_conv_op.cpp:258-262) out of the max|mu| it reads
+ * back on every call; this library reads nothing back unless asked. */
+dau_status_t dau_take_nan_flag(dau_handle_t* h, int* found, void* stream);
+
 /* Fused epilogue / prologue (the steps the reference's Python layer runs right after the op:
  * bias add and activation, plugins/tensorflow/dau_conv/dau_conv.py:500-526; ReLU is what every
  * reference model uses).  With DAU_ACT_RELU dau_forward stores max(0, y + bias) and

@@ -463,3 +463,27 @@ def test_corner_based_offsets_equal_centred_ones():
     for a, b in zip(*res):
         assert np.array_equal(a, b)
     close(res[1][0], O.forward(x, w, mu1, mu2, [0.5]), "y")
+
+
+def test_nan_offsets_are_flagged_and_contribute_nothing():
+    """A NaN mu makes the TF op fail the call (dau_conv_op.cpp:258-262).  Here the unit is dropped
+    (w = 0) and a sticky flag is raised that dau_take_nan_flag reads and clears; dau_conv_op(check_nan=True)
+    turns it into the op's error."""
+    import torch
+    import dau_conv
+    x, err, w, mu1, mu2, ks = _case((2, 20, 12, 3, 4, (1, 2), 9, 3), 9)
+    dev = torch.device("cuda:0")
+    sig = np.full(w.shape, 0.5, np.float32)
+    bad = mu1.copy(); bad[0, 1, 0, 2] = np.nan
+    w0 = w.copy(); w0[0, 1, 0, 2] = 0.0
+    a = dict(num_output=4, number_units_x=1, number_units_y=2, kernel_size=ks, pad=4)
+    t = lambda *arrs: [torch.from_numpy(np.ascontiguousarray(v)).to(dev) for v in arrs]
+    h = dau_conv.get_handle(dev, **a)
+    h.take_nan_flag()
+    y = dau_conv.dau_conv_op(*t(x, w, bad, mu2, sig), sigma_value=0.5, **a)
+    assert h.take_nan_flag() and not h.take_nan_flag()           # raised once, cleared by the read
+    close(y.cpu().numpy(), O.forward(x, w0, mu1, mu2, [0.5]), "y without the NaN unit")
+    dau_conv.dau_conv_op(*t(x, w, mu1, mu2, sig), sigma_value=0.5, **a)
+    assert not h.take_nan_flag()
+    with pytest.raises(RuntimeError):
+        dau_conv.dau_conv_op(*t(x, w, bad, mu2, sig), sigma_value=0.5, check_nan=True, **a)
