@@ -189,7 +189,7 @@ dau_gather_tma_kernel(const __grid_constant__ CUtensorMap in_map, const TGatherP
             const uint32_t tx_bytes = ((p.debug & 2) ? 0 : GEO::TILE_BYTES) + ((p.debug & 4) ? 0 : nrec * (uint32_t)sizeof(UnitRec));
             for (int ci = ci_begin; ci < ci_end; ++ci) {
                 const int st = (ci - ci_begin) % nstage, use = (ci - ci_begin) / nstage;
-                if (use > 0) mbar_wait(&empty_bar[st], (use - 1) & 1);
+                if (use > 0) mbar_wait_backoff(&empty_bar[st], (use - 1) & 1);
                 unsigned char* dst = smem_raw + (size_t)st * p.stage_bytes;
                 mbar_arrive_expect_tx(&full_bar[st], tx_bytes);
                 if (!(p.debug & 2)) tensor4_g2s(dst, &in_map, 2 * ((x0 - GEO::HX) / 4), 0, y0 - GEO::HY, np * p.Cin + ci, &full_bar[st]);

@@ -151,11 +151,11 @@ dau_grad_tma_kernel(const __grid_constant__ CUtensorMap err_map, const TGradPara
                 const int k = item - item_begin, st = k & 1, use = k >> 1;
                 const int n = item / p.tiles, t = item - n * p.tiles;   // n = image pair
                 const int tyi = t / p.tiles_x, txi = t - tyi * p.tiles_x;
-                if (k > 0) mbar_wait(&xempty_bar, (k - 1) & 1);
+                if (k > 0) mbar_wait_backoff(&xempty_bar, (k - 1) & 1);
                 mbar_arrive_expect_tx(&xfull_bar, tx_x);
                 if (!(p.debug & 4)) bulk_g2s(xdst, p.xs + ((size_t)item * p.S + s0) * (XK_WARP_BYTES / 4),
                                              nsv * XK_WARP_BYTES, &xfull_bar);
-                if (use > 0) mbar_wait(&empty_bar[st], (use - 1) & 1);
+                if (use > 0) mbar_wait_backoff(&empty_bar[st], (use - 1) & 1);
                 unsigned char* dst = smem_raw + (size_t)st * p.stage_bytes;
                 mbar_arrive_expect_tx(&full_bar[st], tx_e);
                 for (int fi = 0; fi < nfeat && !(p.debug & 2); ++fi)

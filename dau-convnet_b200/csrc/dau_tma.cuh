@@ -71,6 +71,11 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     while (!mbar_try_wait(bar, parity)) { }
 }
+// Wait of a PRODUCER lane: it shares a scheduler with two consumer warps and waits most of the time,
+// so it sleeps between polls instead of spending that scheduler's issue slots on try_wait + branch.
+__device__ __forceinline__ void mbar_wait_backoff(uint64_t* bar, uint32_t parity) {
+    while (!mbar_try_wait(bar, parity)) { __nanosleep(128); }
+}
 
 // 1-D bulk copy global -> shared (bytes multiple of 16, both addresses 16-byte aligned)
 __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
