@@ -107,6 +107,12 @@ dau_status_t dau_set_sigma_hint(dau_handle_t* h, float value) {
     return DAU_OK;
 }
 
+dau_status_t dau_set_offset_hint(dau_handle_t* h, float max_abs_offset) {
+    if (!h) return fail(DAU_ERR_INVALID_ARGUMENT, "dau_set_offset_hint: NULL handle");
+    h->layer->set_offset_hint(max_abs_offset);
+    return DAU_OK;
+}
+
 dau_status_t dau_forward(dau_handle_t* h, const float* bottom, float* w, float* mu1, float* mu2,
                          float* sigma, const float* bias, float* top, void* ws, size_t ws_bytes,
                          void* stream) {

@@ -115,12 +115,20 @@ void DAUConvLayerB200::Reshape(int N, int S, int H, int W, size_t* fwd_ws, size_
     const size_t units = (size_t)S * G_ * F_;
     // TMA + FFMA2 kernels on the (mosaic) pair layouts
     const float sig = sigma_hint_ > 0.f ? sigma_hint_ : 0.5f;      // the op's default sigma (dau_conv.py:296-297)
-    const int gap = std::max(max_off_, blur_kernel_size(sig) / 2);
+    // displacement bucket: the whole kernel_size/2 unless the caller bounded |mu| (set_offset_hint):
+    // the reference's op picks its kernel from max|mu| on every call (dau_conv_op.cpp:222-256,
+    // buckets 9 / 17 / 33 / 65 = displacement < 4 / 8 / 16 / 32)
+    eff_off_ = max_off_;
+    if (offset_hint_ >= 0.f) {
+        for (int c : {4, 8, 16, 32})
+            if (offset_hint_ < (float)c && c < eff_off_) { eff_off_ = c; break; }
+    }
+    const int gap = std::max(eff_off_, blur_kernel_size(sig) / 2);
     mosaic_ = plan_mosaic(N, H, W, gap);
     const Mosaic& m = mosaic_;
-    DAU_CHECK(plan_gather_tma(m.Nv, S, F_, G_, m.Hv, m.Wv, max_off_, num_sms_, &fwd_plan_), 4, "no forward gather plan for this shape");
-    DAU_CHECK(plan_gather_tma(m.Nv, F_, S, G_, m.Hv, m.Wv, max_off_, num_sms_, &bwd_plan_), 4, "no back-propagation gather plan for this shape");
-    DAU_CHECK(plan_grad_tma(m.Nv, S, F_, G_, m.Hv, m.Wv, max_off_, num_sms_, &grad_plan_), 4, "no gradient plan for this shape");
+    DAU_CHECK(plan_gather_tma(m.Nv, S, F_, G_, m.Hv, m.Wv, eff_off_, num_sms_, &fwd_plan_), 4, "no forward gather plan for this shape");
+    DAU_CHECK(plan_gather_tma(m.Nv, F_, S, G_, m.Hv, m.Wv, eff_off_, num_sms_, &bwd_plan_), 4, "no back-propagation gather plan for this shape");
+    DAU_CHECK(plan_grad_tma(m.Nv, S, F_, G_, m.Hv, m.Wv, eff_off_, num_sms_, &grad_plan_), 4, "no gradient plan for this shape");
     // forward workspace: blurred input | unit table | partial strips of the gather's split tail
     size_t o = 0;
     const size_t blur_in = paired_layout_floats(m.Nv, S, m.Hv, m.Wv);
@@ -245,7 +253,7 @@ void DAUConvLayerB200::Forward_gpu(const float* bottom, float* w, float* mu1, fl
     UnitPrepArgs ua;
     ua.w = w; ua.mu1 = mu1; ua.mu2 = mu2; ua.S = S_; ua.G = G_; ua.F = F_;
     ua.g_active = G_ - st_.number_units_ignore;
-    ua.halo_x = fwd_plan_.halo_x; ua.halo_y = fwd_plan_.halo_y; ua.max_off = max_off_;
+    ua.halo_x = fwd_plan_.halo_x; ua.halo_y = fwd_plan_.halo_y; ua.max_off = eff_off_;
     ua.ghalo_x = ua.halo_x; ua.ghalo_y = ua.halo_y;
     ua.use_interpolation = st_.use_interpolation; ua.mu_center = mu_center();
     launch_unit_prep(ua, table, nullptr, nullptr, nan_flag_, stream);
@@ -288,7 +296,7 @@ void DAUConvLayerB200::Backward_gpu(const float* bottom, const float* top_error,
     UnitPrepArgs ua;
     ua.w = w; ua.mu1 = mu1; ua.mu2 = mu2; ua.S = S_; ua.G = G_; ua.F = F_;
     ua.g_active = G_ - st_.number_units_ignore;
-    ua.max_off = max_off_; ua.use_interpolation = st_.use_interpolation; ua.mu_center = mu_center();
+    ua.max_off = eff_off_; ua.use_interpolation = st_.use_interpolation; ua.mu_center = mu_center();
 
     if (want_params) {
         tic(1, 0, stream);

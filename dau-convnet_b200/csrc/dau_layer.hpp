@@ -44,6 +44,10 @@ public:
     // reference reads it once in LayerSetUp, base_dau_conv_layer.hpp:266-275).  Reshape sizes the
     // mosaic gap from it, so set it BEFORE Reshape when sigma is larger than the op default 0.5.
     void set_sigma_hint(float v) { sigma_hint_ = v; }
+    // max|mu - centre| known to the caller (set BEFORE Reshape; negative = unknown): the halos, the
+    // mosaic gap and the clamp of the integer offsets shrink to the displacement bucket (< 4, 8, 16,
+    // 32) that holds it, the per-call choice the reference's op makes from max|mu| (dau_conv_op.cpp:222-256)
+    void set_offset_hint(float v) { offset_hint_ = v; }
     // true if any mu was NaN in a forward / backward call since the last query (such units are
     // treated as w = 0); blocks on `stream`.  The TF op fails the call instead (dau_conv_op.cpp:258-262)
     // because it reads max|mu| back on every call anyway; here the read is the caller's choice.
@@ -74,7 +78,8 @@ private:
 
     dau_settings_t st_;
     int device_, num_sms_;
-    int N_ = 0, S_ = 0, H_ = 0, W_ = 0, F_ = 0, G_ = 0, max_off_ = 0;
+    int N_ = 0, S_ = 0, H_ = 0, W_ = 0, F_ = 0, G_ = 0, max_off_ = 0, eff_off_ = 0;
+    float offset_hint_ = -1.f;
     bool shaped_ = false;
     GatherPlan fwd_plan_{}, bwd_plan_{};
     GradPlan grad_plan_{};

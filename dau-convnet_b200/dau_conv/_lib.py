@@ -12,7 +12,7 @@ LIB_PATH = os.path.join(_HERE, "libdau_conv_b200.so")
 # exported symbols, in the order of include/dau_conv_b200.h (checked by tests/test_capi.py)
 SYMBOLS = [
     "dau_last_error", "dau_abi_version", "dau_settings_default", "dau_create", "dau_destroy",
-    "dau_reshape", "dau_get_output_size", "dau_set_sigma_hint", "dau_forward", "dau_backward", "dau_set_activation", "dau_backward_act", "dau_take_nan_flag",
+    "dau_reshape", "dau_get_output_size", "dau_set_sigma_hint", "dau_set_offset_hint", "dau_forward", "dau_backward", "dau_set_activation", "dau_backward_act", "dau_take_nan_flag",
     "dau_get_kernels",
     "dau_forward_host", "dau_backward_host", "dau_train_step_host", "dau_plan_mosaic", "dau_mosaic_to_real", "dau_measure_fma_peak", "dau_enable_timing",
     "dau_get_timing", "dau_timing_name", "dau_launch_count",
@@ -58,6 +58,7 @@ lib.dau_destroy.restype = None
 lib.dau_reshape.argtypes = [_vp, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]
 lib.dau_get_output_size.argtypes = [_vp, C.POINTER(C.c_int), C.POINTER(C.c_int)]
 lib.dau_set_sigma_hint.argtypes = [_vp, C.c_float]
+lib.dau_set_offset_hint.argtypes = [_vp, C.c_float]
 lib.dau_forward.argtypes = [_vp] + [_vp] * 7 + [_vp, C.c_size_t, _vp]
 lib.dau_backward.argtypes = [_vp] + [_vp] * 12 + [C.c_uint, _vp, C.c_size_t, _vp]
 lib.dau_take_nan_flag.argtypes = [_vp, C.POINTER(C.c_int), _vp]

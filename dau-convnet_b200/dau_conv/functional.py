@@ -69,6 +69,7 @@ class DAULayerHandle(object):
         _lib.check(_lib.lib.dau_create(C.byref(settings), idx, C.byref(self._h)))
         self._shape = None
         self._hint = None
+        self._off_hint = -1.0
         self._ws = None
         self.fwd_bytes = self.bwd_bytes = 0
 
@@ -82,11 +83,11 @@ class DAULayerHandle(object):
 
     def reshape(self, N, S, H, W):
         # the layer plans its layouts (mosaic gap) from the shape AND the blur width, i.e. sigma
-        if self._shape != (N, S, H, W, self._hint):
+        if self._shape != (N, S, H, W, self._hint, self._off_hint):
             f, b = C.c_size_t(0), C.c_size_t(0)
             _lib.check(_lib.lib.dau_reshape(self._h, N, S, H, W, C.byref(f), C.byref(b)))
             self.fwd_bytes, self.bwd_bytes = f.value, b.value
-            self._shape = (N, S, H, W, self._hint)
+            self._shape = (N, S, H, W, self._hint, self._off_hint)
             ho, wo = C.c_int(0), C.c_int(0)
             _lib.check(_lib.lib.dau_get_output_size(self._h, C.byref(ho), C.byref(wo)))
             self.out_hw = (ho.value, wo.value)      # == (H, W) unless pad < (kernel_size-1)/2
@@ -103,6 +104,14 @@ class DAULayerHandle(object):
         if value != self._hint:
             _lib.check(_lib.lib.dau_set_sigma_hint(self._h, value))
             self._hint = value
+
+    def set_offset_hint(self, max_abs_offset):
+        """Upper bound of |mu| (None / negative: unknown): the layer then plans for the displacement
+        bucket < 4 / 8 / 16 / 32 that holds it instead of kernel_size/2 (dau_conv_op.cpp:222-256)."""
+        value = -1.0 if max_abs_offset is None else float(max_abs_offset)
+        if value != self._off_hint:
+            _lib.check(_lib.lib.dau_set_offset_hint(self._h, value))
+            self._off_hint = value
 
     def enable_timing(self, enable=True):
         _lib.check(_lib.lib.dau_enable_timing(self._h, int(enable)))
@@ -225,12 +234,13 @@ def _sigma_of(sigma, sigma_value):
     return float(sigma.reshape(-1)[0]) if sigma_value is None else float(sigma_value)
 
 
-def dau_conv_op(input, weights, mu1, mu2, sigma, sigma_value=None, check_nan=False, **attrs):
+def dau_conv_op(input, weights, mu1, mu2, sigma, sigma_value=None, check_nan=False, max_offset=None, **attrs):
     """TF op DAUConv: output[N,F,H,W] (forward only, no autograd).  check_nan=True reproduces the op's
     FAILED_PRECONDITION on NaN offsets (dau_conv_op.cpp:258-262) at the price of one host sync."""
     _check_inputs(input, weights, mu1, mu2, sigma, attrs)
     h = get_handle(input.device, **attrs)
     h.set_sigma_hint(_sigma_of(sigma, sigma_value))
+    h.set_offset_hint(max_offset)
     out = h.forward(input.contiguous(), weights.contiguous(), mu1.contiguous(), mu2.contiguous(),
                     sigma.contiguous())
     if check_nan and h.take_nan_flag():
@@ -238,11 +248,12 @@ def dau_conv_op(input, weights, mu1, mu2, sigma, sigma_value=None, check_nan=Fal
     return out
 
 
-def dau_conv_grad_op(grad, input, weights, mu1, mu2, sigma, sigma_value=None, **attrs):
+def dau_conv_grad_op(grad, input, weights, mu1, mu2, sigma, sigma_value=None, max_offset=None, **attrs):
     """TF op DAUConvGrad: (grad_input, grad_weights, grad_mu1, grad_mu2, grad_sigma)."""
     _check_inputs(input, weights, mu1, mu2, sigma, attrs)
     h = get_handle(input.device, **attrs)
     h.set_sigma_hint(_sigma_of(sigma, sigma_value))
+    h.set_offset_hint(max_offset)
     return h.backward(input.contiguous(), grad.contiguous(), weights.contiguous(), mu1.contiguous(),
                       mu2.contiguous(), sigma.contiguous())
 
@@ -251,11 +262,12 @@ class _DAUConvFunction(torch.autograd.Function):
     """@ops.RegisterGradient("DAUConv") equivalent (_dau_conv_grad_op.py:14-60)."""
 
     @staticmethod
-    def forward(ctx, input, weights, mu1, mu2, sigma, attrs, sigma_value):
-        ctx.attrs = attrs
+    def forward(ctx, input, weights, mu1, mu2, sigma, attrs, sigma_value, max_offset=None):
+        ctx.attrs, ctx.max_offset = attrs, max_offset
         ctx.sigma_value = _sigma_of(sigma, sigma_value)
         ctx.save_for_backward(input, weights, mu1, mu2, sigma)
-        return dau_conv_op(input, weights, mu1, mu2, sigma, sigma_value=ctx.sigma_value, **attrs)
+        return dau_conv_op(input, weights, mu1, mu2, sigma, sigma_value=ctx.sigma_value, max_offset=max_offset,
+                           **attrs)
 
     @staticmethod
     def backward(ctx, grad):
@@ -269,15 +281,17 @@ class _DAUConvFunction(torch.autograd.Function):
         _check_inputs(input, weights, mu1, mu2, sigma, ctx.attrs)
         h = get_handle(input.device, **ctx.attrs)
         h.set_sigma_hint(ctx.sigma_value)
+        h.set_offset_hint(ctx.max_offset)
         dx, dw, dm1, dm2, dsg = h.backward(input.contiguous(), grad.contiguous(), weights.contiguous(),
                                            mu1.contiguous(), mu2.contiguous(), sigma.contiguous(), flags=flags)
         return (dx if need[0] else None, dw if need[1] else None, dm1 if need[2] else None,
-                dm2 if need[3] else None, dsg if need[4] else None, None, None)
+                dm2 if need[3] else None, dsg if need[4] else None, None, None, None)
 
 
-def dau_conv(input, weights, mu1, mu2, sigma, sigma_value=None, **attrs):
-    """Differentiable DAUConv (forward + registered gradient)."""
-    return _DAUConvFunction.apply(input, weights, mu1, mu2, sigma, attrs, sigma_value)
+def dau_conv(input, weights, mu1, mu2, sigma, sigma_value=None, max_offset=None, **attrs):
+    """Differentiable DAUConv (forward + registered gradient).  max_offset: an upper bound of |mu| the
+    caller knows (plans the displacement bucket from it, see DAULayerHandle.set_offset_hint)."""
+    return _DAUConvFunction.apply(input, weights, mu1, mu2, sigma, attrs, sigma_value, max_offset)
 
 
 class _DAUConvFusedFunction(torch.autograd.Function):
@@ -286,12 +300,13 @@ class _DAUConvFusedFunction(torch.autograd.Function):
     act(y + bias), the backward pass masks the incoming gradient as it loads it."""
 
     @staticmethod
-    def forward(ctx, input, weights, mu1, mu2, sigma, bias, attrs, sigma_value, activation):
-        ctx.attrs, ctx.activation = attrs, activation
+    def forward(ctx, input, weights, mu1, mu2, sigma, bias, attrs, sigma_value, activation, max_offset=None):
+        ctx.attrs, ctx.activation, ctx.max_offset = attrs, activation, max_offset
         ctx.sigma_value = _sigma_of(sigma, sigma_value)
         _check_inputs(input, weights, mu1, mu2, sigma, attrs)
         h = get_handle(input.device, **attrs)
         h.set_sigma_hint(ctx.sigma_value)
+        h.set_offset_hint(max_offset)
         out = h.forward(input.contiguous(), weights.contiguous(), mu1.contiguous(), mu2.contiguous(),
                         sigma.contiguous(), bias=bias.contiguous() if bias is not None else None,
                         activation=activation)
@@ -313,18 +328,20 @@ class _DAUConvFusedFunction(torch.autograd.Function):
             dbias = torch.zeros(weights.shape[-1], dtype=torch.float32, device=grad.device)
         h = get_handle(input.device, **ctx.attrs)
         h.set_sigma_hint(ctx.sigma_value)
+        h.set_offset_hint(ctx.max_offset)
         dx, dw, dm1, dm2, dsg = h.backward(input.contiguous(), grad.contiguous(), weights.contiguous(),
                                            mu1.contiguous(), mu2.contiguous(), sigma.contiguous(), flags=flags,
                                            dbias=dbias, top_data=out, activation=ctx.activation)
         return (dx if need[0] else None, dw if need[1] else None, dm1 if need[2] else None,
-                dm2 if need[3] else None, dsg if need[4] else None, dbias, None, None, None)
+                dm2 if need[3] else None, dsg if need[4] else None, dbias, None, None, None, None)
 
 
-def dau_conv_fused(input, weights, mu1, mu2, sigma, bias=None, activation=None, sigma_value=None, **attrs):
+def dau_conv_fused(input, weights, mu1, mu2, sigma, bias=None, activation=None, sigma_value=None, max_offset=None,
+                   **attrs):
     """Differentiable act(DAUConv(input) + bias) in ONE pass of the operator (SURVEY section 8
     row f3).  activation: None or "relu"."""
     if activation not in (None, "relu"):
         raise ValueError("dau_conv_fused: activation must be None or 'relu'")
     attrs = dict(attrs, bias_term=bias is not None)
     act = _lib.ACT_RELU if activation == "relu" else _lib.ACT_NONE
-    return _DAUConvFusedFunction.apply(input, weights, mu1, mu2, sigma, bias, attrs, sigma_value, act)
+    return _DAUConvFusedFunction.apply(input, weights, mu1, mu2, sigma, bias, attrs, sigma_value, act, max_offset)

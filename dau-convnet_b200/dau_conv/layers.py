@@ -73,7 +73,7 @@ class DAUConv2d(nn.Module):
                  mu2_initializer=None, sigma_initializer=None, bias_initializer=None,
                  mu_learning_rate_factor=500, dau_unit_border_bound=0.01, dau_unit_single_dim=False,
                  dau_aggregation_forbid_positive_dim1=False, dau_sigma_trainable=False,
-                 dau_mu_interpolation=True, unit_testing=False, in_channels=None):
+                 dau_mu_interpolation=True, unit_testing=False, in_channels=None, dynamic_kernel_size=False):
         super().__init__()
         if data_format != "channels_first":
             raise ValueError("Only `channels_first` supported, i.e., NCHW format.")      # :374-376
@@ -92,6 +92,9 @@ class DAUConv2d(nn.Module):
         self.dau_sigma_trainable = dau_sigma_trainable
         self.dau_mu_interpolation = dau_mu_interpolation
         self.unit_testing = unit_testing
+        # True: read max|mu| back on every call and plan the displacement bucket that holds it, what the
+        # reference's op does (dau_conv_op.cpp:222-256); False (default): plan for max_kernel_size, no sync
+        self.dynamic_kernel_size = bool(dynamic_kernel_size)
         # odd unit counts get dummy units with zero weight (:311-327)
         self.num_dau_units_all = self.dau_units[0] * self.dau_units[1]
         self.num_dau_units_ignore = 0
@@ -179,6 +182,8 @@ class DAUConv2d(nn.Module):
         relu = self.activation in (torch.relu, nn.functional.relu) or isinstance(self.activation, nn.ReLU)
         out = Fn.dau_conv_fused(inputs, self.weights, mu1, mu2, sigma, bias=self.bias if self.use_bias else None,
                                 activation="relu" if relu else None, sigma_value=self._sigma_value,
+                                max_offset=(float(torch.maximum(mu1.detach().abs().max(), mu2.detach().abs().max()))
+                                            if self.dynamic_kernel_size else None),
                                 **self._op_attrs())
         if self.strides > 1:                                  # emulated by slicing (:496-498)
             out = out[:, :, ::self.strides, ::self.strides]

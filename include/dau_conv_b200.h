@@ -97,6 +97,13 @@ dau_status_t dau_reshape(dau_handle_t* h, int N, int S, int H, int W,
  * value <= 0 re-enables the read. */
 dau_status_t dau_set_sigma_hint(dau_handle_t* h, float value);
 
+/* Optional, BEFORE dau_reshape: an upper bound of |mu - centre| over all units.  The halos, the
+ * mosaic gap and the clamp of the integer offsets then follow the displacement bucket (< 4, 8, 16
+ * or 32 pixels) that holds the bound instead of kernel_size/2 -- the choice the reference's TF op
+ * makes on every call from max|mu| (dau_conv_op.cpp:222-256: kernel 9 / 17 / 33 / 65), here without
+ * the device read.  Offsets beyond the bucket are clamped.  A negative value removes the bound. */
+dau_status_t dau_set_offset_hint(dau_handle_t* h, float max_abs_offset);
+
 /* Output size after dau_reshape: H_out = H + 2*pad - kernel_size + 1 (base_dau_conv_layer.cpp:20-22).
  * pad == (kernel_size-1)/2 (what the TF op always passes) gives H_out == H; a smaller pad gives the
  * centre of the same-size result, and the backward pass takes top_error[N,F,H_out,W_out] as if

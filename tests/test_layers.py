@@ -85,3 +85,25 @@ def test_functional_wrapper_normaliser_replaces_bias():
     assert layer.bias is None and out.shape == (2, 4, 12, 12) and float(out.detach().min()) >= 0.0
     out2, _ = dau_conv2d(x, 4, (2, 2), 9, layer=layer, activation_fn=None, normalizer_fn=None)
     np.testing.assert_allclose(torch.relu(2.0 * out2).detach().cpu().numpy(), out.detach().cpu().numpy(), rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.gpu
+def test_dynamic_kernel_size_matches_the_static_plan():
+    """DAUConv2d(dynamic_kernel_size=True) reads max|mu| and plans its bucket (dau_conv_op.cpp:222-256)."""
+    import torch
+    import dau_conv
+    torch.manual_seed(3)
+    dev = torch.device("cuda:0")
+    x = torch.rand(4, 6, 24, 24, device=dev)
+    a = dau_conv.DAUConv2d(8, (1, 2), 33, in_channels=6, activation=torch.relu).to(dev)
+    b = dau_conv.DAUConv2d(8, (1, 2), 33, in_channels=6, activation=torch.relu, dynamic_kernel_size=True).to(dev)
+    b.load_state_dict(a.state_dict())
+    with torch.no_grad():
+        a.mu1.uniform_(-3, 3); a.mu2.uniform_(-3, 3)
+        b.mu1.copy_(a.mu1); b.mu2.copy_(a.mu2)
+    ya, yb = a(x), b(x)
+    ya.square().sum().backward(); yb.square().sum().backward()
+    assert torch.allclose(ya, yb, rtol=1e-4, atol=1e-5)
+    for pa, pb in zip(a.parameters(), b.parameters()):
+        if pa.grad is not None:
+            assert torch.allclose(pa.grad, pb.grad, rtol=1e-3, atol=1e-4 * float(pa.grad.abs().max()))

@@ -487,3 +487,40 @@ def test_nan_offsets_are_flagged_and_contribute_nothing():
     assert not h.take_nan_flag()
     with pytest.raises(RuntimeError):
         dau_conv.dau_conv_op(*t(x, w, bad, mu2, sig), sigma_value=0.5, check_nan=True, **a)
+
+
+def test_offset_hint_selects_the_displacement_bucket():
+    """dau_set_offset_hint: with max_kernel_size 33 and |mu| < 3.9 the layer plans the '< 4' bucket the
+    reference's op would pick from max|mu| (dau_conv_op.cpp:222-256): same results as the full-kernel
+    plan within the tolerance (the tiling differs), much smaller gaps and halos; offsets beyond a
+    too-small bound are clamped into its bucket, not undefined."""
+    import torch
+    import dau_conv
+    x, err, w, mu1, mu2, _ = _case((6, 27, 27, 5, 6, (1, 2), 9, 3.9), 31)
+    dev = torch.device("cuda:0")
+    sig = np.full(w.shape, 0.5, np.float32)
+    t = [torch.from_numpy(np.ascontiguousarray(v)).to(dev) for v in (x, w, mu1, mu2, sig)]
+    e = torch.from_numpy(err).to(dev)
+    a = dict(num_output=6, number_units_x=1, number_units_y=2, kernel_size=33, pad=16, unit_testing=True)
+    h = dau_conv.get_handle(dev, **a)
+    y_ref = O.forward(x, w, mu1, mu2, [0.5])
+    g_ref = O.backward(x, err, w, mu1, mu2, [0.5], ignore_edge_gradients=True)
+    sizes = []
+    for bound in (None, 3.95):
+        y = dau_conv.dau_conv_op(*t, sigma_value=0.5, max_offset=bound, **a)
+        grads = dau_conv.dau_conv_grad_op(e, *t, sigma_value=0.5, max_offset=bound, **a)
+        torch.cuda.synchronize()
+        close(y.cpu().numpy(), y_ref, "y bound=%s" % bound)
+        for name, got, want in zip(["dx", "dw", "dmu1", "dmu2", "dsigma"], grads, g_ref):
+            close(got.cpu().numpy(), want, name, scale_atol=name != "dx")
+        sizes.append((h.fwd_bytes, h.bwd_bytes))
+    assert sizes[0] != sizes[1]                    # a different plan (gap 4 instead of 16) really ran
+    # a bound that is too small clamps the integer offsets into its bucket [-4, 3]
+    big1, big2 = (3 * mu1).astype(np.float32), (3 * mu2).astype(np.float32)
+    tb = [torch.from_numpy(v).to(dev) for v in (big1, big2)]
+    y = dau_conv.dau_conv_op(t[0], t[1], tb[0], tb[1], t[4], sigma_value=0.5, max_offset=3.0, **a)
+
+    def clamp(m):        # what split_offset does: floor clamped to [-4, 3], fraction 0 / 1 at the ends
+        return np.clip(m, -4.0, 4.0).astype(np.float32)
+    close(y.cpu().numpy(), O.forward(x, w, clamp(big1), clamp(big2), [0.5]), "y with clamped offsets")
+    h.set_offset_hint(None)
