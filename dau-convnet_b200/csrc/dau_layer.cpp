@@ -83,9 +83,10 @@ DAUConvLayerB200::DAUConvLayerB200(const dau_settings_t& s, int device) : st_(s)
     DAU_CHECK(s.number_units_ignore >= 0 && s.number_units_ignore < G_ + 1, 1, "number_units_ignore out of range");
     F_ = s.num_output;
     max_off_ = s.kernel_size / 2;
-    DAU_CUDA_CHECK(cudaSetDevice(device));
+    if (device_ < 0) DAU_CUDA_CHECK(cudaGetDevice(&device_));   // negative = the caller's current device
+    DAU_CUDA_CHECK(cudaSetDevice(device_));
     cudaDeviceProp prop;
-    DAU_CUDA_CHECK(cudaGetDeviceProperties(&prop, device));
+    DAU_CUDA_CHECK(cudaGetDeviceProperties(&prop, device_));
     DAU_CHECK(prop.major >= 10, 4, "this library is built for sm_100a (B200) only");
     num_sms_ = prop.multiProcessorCount;
     // sticky "a mu was NaN" flag, read and cleared by take_nan_flag()

@@ -84,6 +84,7 @@ const char* dau_last_error(void);          /* thread-local message of the last f
 int         dau_abi_version(void);
 void        dau_settings_default(dau_settings_t* s);
 
+/* device: CUDA ordinal; negative = the calling thread's current device */
 dau_status_t dau_create(const dau_settings_t* settings, int device, dau_handle_t** out);
 void         dau_destroy(dau_handle_t* h);
 
