@@ -1,0 +1,54 @@
+"""ctypes binding of oracle/_ref/libdau_ref_cuda.so: the REFERENCE's own CUDA path
+(BaseDAUConvLayer<float>::Forward_gpu / Backward_gpu) compiled for sm_100a from the sources under
+/root/reference by oracle/Makefile.refcuda, behind the plain-cudaMalloc host of oracle/ref_driver.cpp.
+Test infrastructure: used by tests/test_reference_cuda.py (parity of this repo's kernels against the
+reference's) and tools/ref_cuda_time.py (the reference's kernels timed on the same B200)."""
+import ctypes
+import os
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+SO = os.path.join(ROOT, "oracle", "_ref", "libdau_ref_cuda.so")
+
+
+def available():
+    return os.path.exists(SO)
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        _lib = ctypes.CDLL(SO)
+        fp, i = ctypes.c_void_p, ctypes.c_int
+        _lib.dau_ref_cuda_run.argtypes = [i] * 10 + [ctypes.c_float] + [fp] * 12 + [
+            i, ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_size_t),
+            ctypes.c_char_p, i]
+        _lib.dau_ref_cuda_run.restype = i
+    return _lib
+
+
+def run(x, err, w, mu1, mu2, sigma, units, kernel_size=9, ignore_edge_gradients=True, units_ignore=0,
+        mu_learning_rate_factor=1.0, iters=1):
+    """x, err, w, mu1, mu2, sigma: contiguous fp32 CUDA tensors (NCHW, [1,S,G,F]).  Returns
+    (y, dx, dw, dmu1, dmu2, dsigma, info) as CUDA tensors; info = fwd/bwd ms per pass and workspace bytes."""
+    import torch
+    N, S, H, W = x.shape
+    F = w.shape[3]
+    gx, gy = units
+    assert gx * gy == w.shape[2]
+    y = torch.empty((N, F, H, W), device=x.device, dtype=torch.float32)
+    dx = torch.empty_like(x)
+    grads = [torch.zeros_like(w) for _ in range(4)]
+    fwd, bwd, ws = ctypes.c_float(0), ctypes.c_float(0), ctypes.c_size_t(0)
+    msg = ctypes.create_string_buffer(1024)
+    torch.cuda.synchronize()
+    rc = lib().dau_ref_cuda_run(N, S, F, gx, gy, H, W, kernel_size, int(ignore_edge_gradients), units_ignore,
+                                mu_learning_rate_factor,
+                                *[t.data_ptr() for t in (x, err, w, mu1, mu2, sigma, y, dx, *grads)],
+                                iters, ctypes.byref(fwd), ctypes.byref(bwd), ctypes.byref(ws), msg, 1024)
+    if rc != 0:
+        raise RuntimeError("reference CUDA path failed: " + msg.value.decode(errors="replace"))
+    torch.cuda.synchronize()
+    return (y, dx, *grads, dict(fwd_ms=fwd.value, bwd_ms=bwd.value, workspace_bytes=ws.value))
