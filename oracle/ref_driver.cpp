@@ -195,12 +195,16 @@ extern "C" int dau_ref_cuda_run(int N, int S, int F, int Gx, int Gy, int H, int 
                 CUDA_CHECK(cudaDeviceSynchronize());
                 CUDA_CHECK(cudaEventRecord(e0, stream));
                 layer.Forward_gpu(x, bottom, y, top);
+                // the layer also works on four side streams of its own (base_dau_conv_layer.cpp:168-171): wait for
+                // the whole device before each stamp so that nothing escapes the timed spans
+                CUDA_CHECK(cudaDeviceSynchronize());
                 CUDA_CHECK(cudaEventRecord(e1, stream));
                 layer.Backward_gpu(nullptr, top_error, top, true, x, dx, bottom, {true, true, true, true, false});
                 if (mu_learning_rate_factor != 1.0f) {
                     caffe_gpu_scal<float>((int)P, mu_learning_rate_factor, dmu1, cublas);
                     caffe_gpu_scal<float>((int)P, mu_learning_rate_factor, dmu2, cublas);
                 }
+                CUDA_CHECK(cudaDeviceSynchronize());
                 CUDA_CHECK(cudaEventRecord(e2, stream));
                 CUDA_CHECK(cudaDeviceSynchronize());
                 float a = 0, b = 0;

@@ -1,7 +1,7 @@
 """Parity of this repo's CUDA path against the REFERENCE'S OWN CUDA kernels, both run on the same GPU
 on the same inputs.  oracle/_ref/libdau_ref_cuda.so is the reference's BaseDAUConvLayer<float> built
 for sm_100a from the sources under /root/reference (oracle/Makefile.refcuda; only the kernel-template
-shards for offsets <= 4 px, channel counts that are multiples of 16 and 32- / 64-pixel patches are
+shards for offsets <= 8 px, channel counts that are multiples of 16 and 16- / 32- / 64-pixel patches are
 compiled, so the shapes below stay inside them).
 
 Two bars, both written here:
@@ -43,37 +43,42 @@ def strict(got, ref, name, scale_atol=False):
 
 
 CASES = [
-    # N, S, F, (Gx, Gy), H, W
-    (2, 16, 16, (1, 2), 32, 32),
-    (3, 16, 32, (2, 2), 32, 32),
-    (2, 32, 16, (2, 1), 64, 64),
-    (2, 16, 16, (2, 2), 64, 32),
+    # N, S, F, (Gx, Gy), H, W, kernel_size   (the reference's gradient kernel needs F >= 32)
+    (2, 16, 32, (1, 2), 32, 32, 9),
+    (3, 16, 32, (2, 2), 32, 32, 9),
+    (2, 32, 32, (2, 1), 64, 64, 9),
+    (2, 16, 32, (2, 2), 64, 64, 9),
+    (2, 32, 32, (1, 2), 27, 27, 9),        # AlexNet-DAU L2 map: partial 32x32 patches
+    (4, 16, 32, (1, 2), 13, 13, 9),        # AlexNet-DAU L3-L5 map: 16x16 patches
+    (2, 16, 32, (1, 2), 32, 32, 17),       # offsets up to 8 px (the op's kernel-17 bucket)
+    (2, 32, 64, (1, 2), 28, 28, 17),       # the C4 map
 ]
 
 
-@pytest.mark.parametrize("case", CASES, ids=lambda c: "N%dS%dF%dG%dx%d_%dx%d" % (c[0], c[1], c[2], c[3][0], c[3][1], c[4], c[5]))
+@pytest.mark.parametrize("case", CASES, ids=lambda c: "N%dS%dF%dG%dx%d_%dx%d_k%d" % (c[0], c[1], c[2], c[3][0], c[3][1], c[4], c[5], c[6]))
 def test_matches_reference_cuda(case):
     import torch
     import dau_conv
-    N, S, F, units, H, W = case
+    N, S, F, units, H, W, ks = case
+    m = ks // 2 - 0.01
     G = units[0] * units[1]
     rng = np.random.default_rng(99 + N + S + F + H)
     x = rng.random((N, S, H, W)).astype(np.float32)
     err = rng.standard_normal((N, F, H, W)).astype(np.float32)
     w = (0.1 * rng.standard_normal((1, S, G, F))).astype(np.float32)
-    mu1 = rng.uniform(-3.99, 3.99, (1, S, G, F)).astype(np.float32)
-    mu2 = rng.uniform(-3.99, 3.99, (1, S, G, F)).astype(np.float32)
+    mu1 = rng.uniform(-m, m, (1, S, G, F)).astype(np.float32)
+    mu2 = rng.uniform(-m, m, (1, S, G, F)).astype(np.float32)
     sigma = np.full((1, S, G, F), 0.5, np.float32)
     dev = torch.device("cuda:0")
     t = [torch.from_numpy(a).to(dev) for a in (x, w, mu1, mu2, sigma)]
     te = torch.from_numpy(err).to(dev)
 
-    attrs = dict(num_output=F, number_units_x=units[0], number_units_y=units[1], kernel_size=9, pad=4,
+    attrs = dict(num_output=F, number_units_x=units[0], number_units_y=units[1], kernel_size=ks, pad=(ks - 1) // 2,
                  unit_testing=True, mu_learning_rate_factor=1.0)
     y = dau_conv.dau_conv_op(*t, **attrs).cpu().numpy()
     ours = [y] + [g.cpu().numpy() for g in dau_conv.dau_conv_grad_op(te, *t, **attrs)]
 
-    r = ref_cuda.run(t[0], te, t[1], t[2], t[3], t[4], units, kernel_size=9, ignore_edge_gradients=True)
+    r = ref_cuda.run(t[0], te, t[1], t[2], t[3], t[4], units, kernel_size=ks, ignore_edge_gradients=True)
     ref = [v.cpu().numpy() for v in r[:6]]
 
     names = ["top", "bottom_error", "dw", "dmu1", "dmu2", "dsigma"]
