@@ -5,7 +5,7 @@
 // DAUConvLayerTensorflowGPU / DAUKernel*TF (plugins/tensorflow/src/dau_conv_layer_tensorflow.cpp:
 // 189-276, 347-383, 401-507, 530-556), with cudaMalloc in place of allocate_temp.
 // Linked with the reference's objects into oracle/_ref/libdau_ref_cuda.so by oracle/Makefile.refcuda;
-// only tests/ and tools/ref_cuda_time.py load it.  Nothing here is this repo's product path.
+// only files under tests/ load it.  Nothing here is this repo's product path.
 #include <cstdio>
 #include <cstring>
 #include <string>

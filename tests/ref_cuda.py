@@ -2,7 +2,7 @@
 (BaseDAUConvLayer<float>::Forward_gpu / Backward_gpu) compiled for sm_100a from the sources under
 /root/reference by oracle/Makefile.refcuda, behind the plain-cudaMalloc host of oracle/ref_driver.cpp.
 Test infrastructure: used by tests/test_reference_cuda.py (parity of this repo's kernels against the
-reference's) and tools/ref_cuda_time.py (the reference's kernels timed on the same B200)."""
+reference's) and tests/ref_cuda_time.py (the reference's kernels timed on the same B200)."""
 import ctypes
 import os
 

@@ -3,7 +3,7 @@ oracle/Makefile.refcuda) next to this repo's path: same GPU, same tensors (bench
 input generator).  Prints one JSON line per config; a comparison tool, not bench.py's reference arm
 (that one is the reference's CPU path, as BASELINE.json asks).
 
-usage: python tools/ref_cuda_time.py [--config c2 ...] [--images N]   (default: c2)"""
+usage: python tests/ref_cuda_time.py [--config c2 ...] [--images N]   (default: c2)"""
 import argparse
 import json
 import os
@@ -13,7 +13,7 @@ import numpy as np
 import torch
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-for p in (ROOT, os.path.join(ROOT, "dau-convnet_b200"), os.path.join(ROOT, "tests")):
+for p in (ROOT, os.path.join(ROOT, "dau-convnet_b200"), os.path.dirname(os.path.abspath(__file__))):
     sys.path.insert(0, p)
 import bench  # noqa: E402
 import dau_conv  # noqa: E402
