@@ -98,3 +98,26 @@ def test_matches_reference_cuda(case):
     g_o = O.backward(x, err, w, mu1, mu2, [0.5], ignore_edge_gradients=True)
     strict(ours[0], y_o, "top vs oracle")
     strict(ours[1], g_o[0], "bottom_error vs oracle", scale_atol=True)
+
+
+def test_full_size_c2_matches_reference_cuda():
+    """BASELINE config C2 at its full size (N=128, S=F=128, 64x64, G=4): every output of one forward + backward
+    pass against the reference's CUDA kernels on the same tensors.  Sums run over up to 524 288 terms in different
+    orders on the two sides, so the absolute term of the tolerance is scaled by max(1, max|ref|) for all six."""
+    import torch
+    import bench
+    import dau_conv
+    N, S, F, units, H, W, ks, m = bench.CONFIGS["c2"]
+    G = units[0] * units[1]
+    dev = torch.device("cuda:0")
+    x, e, w, mu1, mu2 = [torch.from_numpy(a).to(dev) for a in bench.make_inputs_numpy("c2", N, 1234)]
+    sigma = torch.full((1, S, G, F), 0.5, device=dev)
+    attrs = dict(num_output=F, number_units_x=units[0], number_units_y=units[1], kernel_size=ks, pad=(ks - 1) // 2,
+                 unit_testing=True, mu_learning_rate_factor=1.0)
+    y = dau_conv.dau_conv_op(x, w, mu1, mu2, sigma, **attrs)
+    g = dau_conv.dau_conv_grad_op(e, x, w, mu1, mu2, sigma, **attrs)
+    r = ref_cuda.run(x, e, w, mu1, mu2, sigma, units, kernel_size=ks, ignore_edge_gradients=True)
+    strict(y[..., :-1, :-1].cpu().numpy(), r[0][..., :-1, :-1].cpu().numpy(), "top (interior)", scale_atol=True)
+    strict(g[0][..., :-1, :-1].cpu().numpy(), r[1][..., :-1, :-1].cpu().numpy(), "bottom_error (interior)", scale_atol=True)
+    for k, name in enumerate(["dw", "dmu1", "dmu2", "dsigma"]):
+        strict(g[1 + k].cpu().numpy(), r[2 + k].cpu().numpy(), name, scale_atol=True)
