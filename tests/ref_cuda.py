@@ -5,6 +5,8 @@ Test infrastructure: used by tests/test_reference_cuda.py (parity of this repo's
 reference's) and tests/ref_cuda_time.py (the reference's kernels timed on the same B200)."""
 import ctypes
 import os
+import subprocess
+import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 SO = os.path.join(ROOT, "oracle", "_ref", "libdau_ref_cuda.so")
@@ -52,3 +54,30 @@ def run(x, err, w, mu1, mu2, sigma, units, kernel_size=9, ignore_edge_gradients=
         raise RuntimeError("reference CUDA path failed: " + msg.value.decode(errors="replace"))
     torch.cuda.synchronize()
     return (y, dx, *grads, dict(fwd_ms=fwd.value, bwd_ms=bwd.value, workspace_bytes=ws.value))
+
+
+class ReferenceFault(RuntimeError):
+    """The reference build refused the shape (exit 3) or died inside its own kernels (any other exit)."""
+
+
+def run_isolated(x, err, w, mu1, mu2, sigma, units, tmp_dir, kernel_size=9, ignore_edge_gradients=True,
+                 units_ignore=0, mu_learning_rate_factor=1.0, iters=1, timeout=300):
+    """Same call on NumPy arrays, in a process of its own (tests/ref_cuda_worker.py): the reference build aborts
+    the process on some shapes, which must not take the test session with it.  Returns NumPy arrays
+    (y, dx, dw, dmu1, dmu2, dsigma, info)."""
+    import numpy as np
+    tmp_dir = str(tmp_dir)
+    np.savez(os.path.join(tmp_dir, "in.npz"), x=x, err=err, w=w, mu1=mu1, mu2=mu2, sigma=sigma,
+             meta=np.array([units[0], units[1], kernel_size, int(ignore_edge_gradients), units_ignore, iters]),
+             mu_lr=np.float32(mu_learning_rate_factor))
+    out = os.path.join(tmp_dir, "out.npz")
+    if os.path.exists(out):
+        os.remove(out)
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "ref_cuda_worker.py"), tmp_dir],
+                       capture_output=True, text=True, timeout=timeout)
+    if r.returncode != 0 or not os.path.exists(out):
+        raise ReferenceFault("exit %d: %s" % (r.returncode, (r.stderr or "").strip()[-400:]))
+    z = np.load(out)
+    f, b, ws = z["info"]
+    return (z["y"], z["dx"], z["dw"], z["dmu1"], z["dmu2"], z["dsigma"],
+            dict(fwd_ms=float(f), bwd_ms=float(b), workspace_bytes=int(ws)))

@@ -1,0 +1,71 @@
+"""Runs ONE call of the reference's CUDA layer (oracle/_ref/libdau_ref_cuda.so) in a process of its own.
+The reference build aborts the process on shapes outside what its authors tested (an exception out of a
+destructor after a faulting kernel), so tests never load it in-process: tests/ref_cuda.py run_isolated()
+spawns this file.  No torch here: device memory through libcudart via ctypes.
+usage: python tests/ref_cuda_worker.py <dir>   (reads <dir>/in.npz, writes <dir>/out.npz)"""
+import ctypes
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+SO = os.path.join(os.path.dirname(HERE), "oracle", "_ref", "libdau_ref_cuda.so")
+
+
+def main():
+    d = sys.argv[1]
+    z = np.load(os.path.join(d, "in.npz"))
+    rt = ctypes.CDLL("libcudart.so.12")
+    rt.cudaMalloc.argtypes = [ctypes.POINTER(ctypes.c_void_p), ctypes.c_size_t]
+    rt.cudaMemcpy.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int]
+    rt.cudaMemset.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_size_t]
+
+    def ck(rc, what):
+        if rc != 0:
+            raise RuntimeError("%s failed with CUDA error %d" % (what, rc))
+
+    def dev(nbytes):
+        p = ctypes.c_void_p()
+        ck(rt.cudaMalloc(ctypes.byref(p), max(nbytes, 4)), "cudaMalloc")
+        ck(rt.cudaMemset(p, 0, max(nbytes, 4)), "cudaMemset")
+        return p
+
+    def up(a):
+        a = np.ascontiguousarray(a, np.float32)
+        p = dev(a.nbytes)
+        ck(rt.cudaMemcpy(p, a.ctypes.data_as(ctypes.c_void_p), a.nbytes, 1), "cudaMemcpy H2D")
+        return p
+
+    def down(p, shape):
+        a = np.empty(shape, np.float32)
+        ck(rt.cudaMemcpy(a.ctypes.data_as(ctypes.c_void_p), p, a.nbytes, 2), "cudaMemcpy D2H")
+        return a
+
+    x, err, w = z["x"], z["err"], z["w"]
+    N, S, H, W = x.shape
+    F = w.shape[3]
+    gx, gy, ks, edge, ignore, iters = [int(v) for v in z["meta"]]
+    px, pe, pw, pm1, pm2, ps = [up(z[k]) for k in ("x", "err", "w", "mu1", "mu2", "sigma")]
+    py, pdx = dev(4 * N * F * H * W), dev(x.nbytes)
+    pg = [dev(w.nbytes) for _ in range(4)]
+    lib = ctypes.CDLL(SO)
+    fp, i = ctypes.c_void_p, ctypes.c_int
+    lib.dau_ref_cuda_run.argtypes = [i] * 10 + [ctypes.c_float] + [fp] * 12 + [
+        i, ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_size_t),
+        ctypes.c_char_p, i]
+    fwd, bwd, ws = ctypes.c_float(0), ctypes.c_float(0), ctypes.c_size_t(0)
+    msg = ctypes.create_string_buffer(1024)
+    rc = lib.dau_ref_cuda_run(N, S, F, gx, gy, H, W, ks, edge, ignore, float(z["mu_lr"]),
+                              px, pe, pw, pm1, pm2, ps, py, pdx, *pg, iters,
+                              ctypes.byref(fwd), ctypes.byref(bwd), ctypes.byref(ws), msg, 1024)
+    if rc != 0:
+        sys.stderr.write("reference CUDA path refused: " + msg.value.decode(errors="replace") + "\n")
+        sys.exit(3)
+    np.savez(os.path.join(d, "out.npz"), y=down(py, (N, F, H, W)), dx=down(pdx, x.shape),
+             dw=down(pg[0], w.shape), dmu1=down(pg[1], w.shape), dmu2=down(pg[2], w.shape),
+             dsigma=down(pg[3], w.shape), info=np.array([fwd.value, bwd.value, float(ws.value)]))
+
+
+if __name__ == "__main__":
+    main()

@@ -1,7 +1,7 @@
 """Parity of this repo's CUDA path against the REFERENCE'S OWN CUDA kernels, both run on the same GPU
 on the same inputs.  oracle/_ref/libdau_ref_cuda.so is the reference's BaseDAUConvLayer<float> built
 for sm_100a from the sources under /root/reference (oracle/Makefile.refcuda; only the kernel-template
-shards for offsets <= 8 px, channel counts that are multiples of 16 and 16- / 32- / 64-pixel patches are
+7 of the 11 forward and 8 of the 17 gradient kernel-template shards are
 compiled, so the shapes below stay inside them).
 
 Two bars, both written here:
@@ -42,6 +42,14 @@ def strict(got, ref, name, scale_atol=False):
         name, int(bad.sum()), bad.size, atol, float(err.max()), float(np.abs(ref).max()))
 
 
+# shapes on which the reference build (as compiled here for sm_100a) itself faults: illegal memory access inside its
+# kernels, process abort.  They stay in the list: this repo is still held to the oracle on them, and the test
+# fails if the reference starts to run them (so that the comparison is switched on).
+REFERENCE_FAULTS = {
+    (2, 15, 32, (1, 2), 32, 32, 9),        # odd S
+    (2, 16, 32, (1, 2), 64, 64, 33),       # the 16-px offset bucket (8 px and 32 px run)
+}
+
 CASES = [
     # N, S, F, (Gx, Gy), H, W, kernel_size   (the reference's gradient kernel needs F >= 32)
     (2, 16, 32, (1, 2), 32, 32, 9),
@@ -52,11 +60,18 @@ CASES = [
     (4, 16, 32, (1, 2), 13, 13, 9),        # AlexNet-DAU L3-L5 map: 16x16 patches
     (2, 16, 32, (1, 2), 32, 32, 17),       # offsets up to 8 px (the op's kernel-17 bucket)
     (2, 32, 64, (1, 2), 28, 28, 17),       # the C4 map
+    (2, 15, 32, (1, 2), 32, 32, 9),        # odd S: the reference's single-subfeature / single-feature kernel variants
+    (2, 16, 32, (1, 2), 64, 32, 9),        # rectangular maps: 32x64 and 64x32 patches
+    (2, 16, 32, (2, 1), 32, 64, 9),
+    (2, 16, 32, (1, 2), 16, 32, 9),
+    (4, 16, 32, (1, 2), 8, 8, 9),          # 8x8 patches
+    (2, 16, 32, (1, 2), 64, 64, 33),       # offsets up to 16 px (kernel 33)
+    (2, 16, 32, (1, 2), 64, 64, 65),       # offsets up to 32 px (kernel 65)
 ]
 
 
 @pytest.mark.parametrize("case", CASES, ids=lambda c: "N%dS%dF%dG%dx%d_%dx%d_k%d" % (c[0], c[1], c[2], c[3][0], c[3][1], c[4], c[5], c[6]))
-def test_matches_reference_cuda(case):
+def test_matches_reference_cuda(case, tmp_path):
     import torch
     import dau_conv
     N, S, F, units, H, W, ks = case
@@ -78,8 +93,21 @@ def test_matches_reference_cuda(case):
     y = dau_conv.dau_conv_op(*t, **attrs).cpu().numpy()
     ours = [y] + [g.cpu().numpy() for g in dau_conv.dau_conv_grad_op(te, *t, **attrs)]
 
-    r = ref_cuda.run(t[0], te, t[1], t[2], t[3], t[4], units, kernel_size=ks, ignore_edge_gradients=True)
-    ref = [v.cpu().numpy() for v in r[:6]]
+    # (3) the oracle arbitrates on the whole maps: this repo's path must be inside tolerance everywhere
+    y_o = O.forward(x, w, mu1, mu2, [0.5])
+    g_o = O.backward(x, err, w, mu1, mu2, [0.5], ignore_edge_gradients=True)
+    strict(ours[0], y_o, "top vs oracle")
+    strict(ours[1], g_o[0], "bottom_error vs oracle", scale_atol=True)
+
+    try:
+        r = ref_cuda.run_isolated(x, err, w, mu1, mu2, sigma, units, tmp_path, kernel_size=ks,
+                                  ignore_edge_gradients=True)
+    except ref_cuda.ReferenceFault as ex:
+        if case in REFERENCE_FAULTS:
+            pytest.xfail("the reference's own CUDA build dies on this shape (%s); this repo matches the oracle" % ex)
+        raise
+    assert case not in REFERENCE_FAULTS, "the reference build now runs this shape: take it off REFERENCE_FAULTS"
+    ref = list(r[:6])
 
     names = ["top", "bottom_error", "dw", "dmu1", "dmu2", "dsigma"]
     # (1) the reference's own rule, its crops
@@ -93,14 +121,9 @@ def test_matches_reference_cuda(case):
     strict(ours[1][..., :-1, :-1], ref[1][..., :-1, :-1], "bottom_error (interior)", scale_atol=True)
     for k in range(2, 6):
         strict(ours[k], ref[k], names[k], scale_atol=True)
-    # (3) the oracle arbitrates on the whole maps: this repo's path must be inside tolerance everywhere
-    y_o = O.forward(x, w, mu1, mu2, [0.5])
-    g_o = O.backward(x, err, w, mu1, mu2, [0.5], ignore_edge_gradients=True)
-    strict(ours[0], y_o, "top vs oracle")
-    strict(ours[1], g_o[0], "bottom_error vs oracle", scale_atol=True)
 
 
-def test_full_size_c2_matches_reference_cuda():
+def test_full_size_c2_matches_reference_cuda(tmp_path):
     """BASELINE config C2 at its full size (N=128, S=F=128, 64x64, G=4): every output of one forward + backward
     pass against the reference's CUDA kernels on the same tensors.  Sums run over up to 524 288 terms in different
     orders on the two sides, so the absolute term of the tolerance is scaled by max(1, max|ref|) for all six."""
@@ -110,14 +133,19 @@ def test_full_size_c2_matches_reference_cuda():
     N, S, F, units, H, W, ks, m = bench.CONFIGS["c2"]
     G = units[0] * units[1]
     dev = torch.device("cuda:0")
-    x, e, w, mu1, mu2 = [torch.from_numpy(a).to(dev) for a in bench.make_inputs_numpy("c2", N, 1234)]
+    host = bench.make_inputs_numpy("c2", N, 1234)
+    x, e, w, mu1, mu2 = [torch.from_numpy(a).to(dev) for a in host]
     sigma = torch.full((1, S, G, F), 0.5, device=dev)
     attrs = dict(num_output=F, number_units_x=units[0], number_units_y=units[1], kernel_size=ks, pad=(ks - 1) // 2,
                  unit_testing=True, mu_learning_rate_factor=1.0)
     y = dau_conv.dau_conv_op(x, w, mu1, mu2, sigma, **attrs)
     g = dau_conv.dau_conv_grad_op(e, x, w, mu1, mu2, sigma, **attrs)
-    r = ref_cuda.run(x, e, w, mu1, mu2, sigma, units, kernel_size=ks, ignore_edge_gradients=True)
-    strict(y[..., :-1, :-1].cpu().numpy(), r[0][..., :-1, :-1].cpu().numpy(), "top (interior)", scale_atol=True)
-    strict(g[0][..., :-1, :-1].cpu().numpy(), r[1][..., :-1, :-1].cpu().numpy(), "bottom_error (interior)", scale_atol=True)
+    y, g = y.cpu().numpy(), [v.cpu().numpy() for v in g]
+    del x, e
+    torch.cuda.empty_cache()
+    r = ref_cuda.run_isolated(*host, np.full((1, S, G, F), 0.5, np.float32), units, tmp_path, kernel_size=ks,
+                              ignore_edge_gradients=True, timeout=600)
+    strict(y[..., :-1, :-1], r[0][..., :-1, :-1], "top (interior)", scale_atol=True)
+    strict(g[0][..., :-1, :-1], r[1][..., :-1, :-1], "bottom_error (interior)", scale_atol=True)
     for k, name in enumerate(["dw", "dmu1", "dmu2", "dsigma"]):
-        strict(g[1 + k].cpu().numpy(), r[2 + k].cpu().numpy(), name, scale_atol=True)
+        strict(g[1 + k], r[2 + k], name, scale_atol=True)
