@@ -56,6 +56,10 @@ def main():
                          "0: one all-reduce of all gradients after backward")
     ap.add_argument("--graph", type=int, default=0,
                     help="1: capture forward + backward + SGD of one rank in a CUDA graph (single GPU only)")
+    ap.add_argument("--lean", type=int, default=1,
+                    help="1: gradients are dropped, not zero-filled, between steps (autograd then assigns instead of "
+                         "accumulating: no fill and no add per parameter) and SGD runs as one fused kernel per "
+                         "parameter group; 0: zero-filled gradients and the foreach SGD")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -76,11 +80,11 @@ def main():
     x = torch.rand((n_local, 3, 227, 227), device=dev, generator=gen)
     target = torch.randint(0, 1000, (n_local,), device=dev, generator=gen)
     params = [p for p in model.parameters() if p.requires_grad]
-    opt = torch.optim.SGD(params, lr=1e-3, momentum=0.9)
+    opt = torch.optim.SGD(params, lr=1e-3, momentum=0.9, fused=bool(args.lean))
     n_dau_units = sum(m.weights.numel() for m in model.modules() if isinstance(m, dau_conv.DAUConv2d))
 
     def step():
-        opt.zero_grad(set_to_none=False)
+        opt.zero_grad(set_to_none=bool(args.lean))
         loss = nn.functional.cross_entropy(net(x), target)
         loss.backward()
         if world > 1 and not args.overlap:                     # one bucket: all gradients, summed, / world
