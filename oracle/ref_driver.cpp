@@ -6,6 +6,7 @@
 // 189-276, 347-383, 401-507, 530-556), with cudaMalloc in place of allocate_temp.
 // Linked with the reference's objects into oracle/_ref/libdau_ref_cuda.so by oracle/Makefile.refcuda;
 // only files under tests/ load it.  Nothing here is this repo's product path.
+#include <cmath>
 #include <cstdio>
 #include <cstring>
 #include <string>
@@ -219,6 +220,46 @@ extern "C" int dau_ref_cuda_run(int N, int S, int F, int Gx, int Gy, int H, int 
         }
         cublasDestroy(cublas);
         cudaStreamDestroy(stream);
+        return 0;
+    } catch (const std::exception& ex) {
+        if (errbuf && errlen > 0) { std::strncpy(errbuf, ex.what(), errlen - 1); errbuf[errlen - 1] = 0; }
+        return -1;
+    }
+}
+
+// DAUKernelCompute alone (row a1): the six Kb x Kb filters the reference derives from sigma for one unit
+// (w = 1, mu = 0), exactly as update_prefiltering_kernels drives it (base_dau_conv_layer.cpp:415-431,
+// :120-126, :165-183).  out_host = [blur, d_w, d_mu1, d_mu2, d_sigma, d_error] (the order of this repo's
+// dau_get_kernels).  flags: 1 single_dimension_kernel, 2 forbid_positive_dim1, 4 no unit normalisation,
+// 8 square unit normalisation.
+extern "C" int dau_ref_cuda_kernels(float sigma, int flags, int* kb_out, float* out_host, int capacity_floats,
+                                    char* errbuf, int errlen) {
+    cublasHandle_t cublas = nullptr;
+    try {
+        const int kb = 2 * (int)ceil(5 * sigma) + 1;
+        if (kb_out) *kb_out = kb;
+        if (capacity_floats < 6 * kb * kb) throw DAUException("ref_driver: output buffer too small");
+        CUBLAS_CHECK(cublasCreate(&cublas));
+        {
+            PlainCompute kc; PlainParams kp; PlainOutput ko;
+            kc.setup(!(flags & 4), (flags & 8) != 0, 0.3f, 0, /*offsets_already_centered=*/true,
+                     (flags & 1) != 0, (flags & 2) != 0);
+            kp.reshape(1, 1, 1);
+            const float one = 1.f, zero = 0.f;
+            CUDA_CHECK(cudaMemcpy(kp.weight(), &one, 4, cudaMemcpyHostToDevice));
+            CUDA_CHECK(cudaMemcpy(kp.mu1(), &zero, 4, cudaMemcpyHostToDevice));
+            CUDA_CHECK(cudaMemcpy(kp.mu2(), &zero, 4, cudaMemcpyHostToDevice));
+            CUDA_CHECK(cudaMemcpy(kp.sigma(), &sigma, 4, cudaMemcpyHostToDevice));
+            kc.reshape(1, 1, 1, kb, kb);
+            ko.reshape(1, 1, 1, kb, kb);
+            kc.get_kernels(kp, ko, /*enable_unit_bounds_guard=*/false, cublas, 0);
+            CUDA_CHECK(cudaDeviceSynchronize());
+            const size_t n = (size_t)kb * kb;
+            CUDA_CHECK(cudaMemcpy(out_host, ko.weight(), 4 * n, cudaMemcpyDeviceToHost));
+            CUDA_CHECK(cudaMemcpy(out_host + n, ko.d_params(), 4 * 4 * n, cudaMemcpyDeviceToHost));
+            CUDA_CHECK(cudaMemcpy(out_host + 5 * n, ko.d_error(), 4 * n, cudaMemcpyDeviceToHost));
+        }
+        cublasDestroy(cublas);
         return 0;
     } catch (const std::exception& ex) {
         if (errbuf && errlen > 0) { std::strncpy(errbuf, ex.what(), errlen - 1); errbuf[errlen - 1] = 0; }

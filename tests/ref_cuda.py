@@ -81,3 +81,16 @@ def run_isolated(x, err, w, mu1, mu2, sigma, units, tmp_dir, kernel_size=9, igno
     f, b, ws = z["info"]
     return (z["y"], z["dx"], z["dw"], z["dmu1"], z["dmu2"], z["dsigma"],
             dict(fwd_ms=float(f), bwd_ms=float(b), workspace_bytes=int(ws)))
+
+
+def kernels_isolated(sigma, flags, tmp_dir, timeout=120):
+    """The reference's DAUKernelCompute::get_kernels for one unit (w = 1, mu = 0) at `sigma`, run in a process of
+    its own: array [6, Kb, Kb] = blur, d_w, d_mu1, d_mu2, d_sigma, d_error.  flags: 1 single_dimension_kernel,
+    2 forbid_positive_dim1, 4 no unit normalisation, 8 square unit normalisation."""
+    import numpy as np
+    out = os.path.join(str(tmp_dir), "kernels_%g_%d.npy" % (sigma, flags))
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "ref_cuda_worker.py"), "--kernels",
+                        repr(float(sigma)), str(int(flags)), out], capture_output=True, text=True, timeout=timeout)
+    if r.returncode != 0 or not os.path.exists(out):
+        raise ReferenceFault("exit %d: %s" % (r.returncode, (r.stderr or "").strip()[-400:]))
+    return np.load(out)

@@ -2,7 +2,8 @@
 The reference build aborts the process on shapes outside what its authors tested (an exception out of a
 destructor after a faulting kernel), so tests never load it in-process: tests/ref_cuda.py run_isolated()
 spawns this file.  No torch here: device memory through libcudart via ctypes.
-usage: python tests/ref_cuda_worker.py <dir>   (reads <dir>/in.npz, writes <dir>/out.npz)"""
+usage: python tests/ref_cuda_worker.py <dir>   (reads <dir>/in.npz, writes <dir>/out.npz)
+       python tests/ref_cuda_worker.py --kernels <sigma> <flags> <out.npy>"""
 import ctypes
 import os
 import sys
@@ -13,7 +14,25 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 SO = os.path.join(os.path.dirname(HERE), "oracle", "_ref", "libdau_ref_cuda.so")
 
 
+def kernels_main(sigma, flags, out_path):
+    """--kernels <sigma> <flags> <out.npy>: the reference's DAUKernelCompute filters for one unit."""
+    lib = ctypes.CDLL(SO)
+    lib.dau_ref_cuda_kernels.argtypes = [ctypes.c_float, ctypes.c_int, ctypes.POINTER(ctypes.c_int), ctypes.c_void_p,
+                                         ctypes.c_int, ctypes.c_char_p, ctypes.c_int]
+    buf = np.zeros(6 * 64 * 64, np.float32)
+    kb = ctypes.c_int(0)
+    msg = ctypes.create_string_buffer(1024)
+    rc = lib.dau_ref_cuda_kernels(sigma, flags, ctypes.byref(kb), buf.ctypes.data_as(ctypes.c_void_p), buf.size, msg, 1024)
+    if rc != 0:
+        sys.stderr.write("reference DAUKernelCompute refused: " + msg.value.decode(errors="replace") + "\n")
+        sys.exit(3)
+    k = kb.value
+    np.save(out_path, buf[:6 * k * k].reshape(6, k, k))
+
+
 def main():
+    if sys.argv[1] == "--kernels":
+        return kernels_main(float(sys.argv[2]), int(sys.argv[3]), sys.argv[4])
     d = sys.argv[1]
     z = np.load(os.path.join(d, "in.npz"))
     rt = ctypes.CDLL("libcudart.so.12")

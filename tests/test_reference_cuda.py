@@ -152,3 +152,20 @@ def test_full_size_c2_matches_reference_cuda(tmp_path):
     strict(g[0][..., :-1, :-1], r[1][..., :-1, :-1], "bottom_error (interior)", scale_atol=True)
     for k, name in enumerate(["dw", "dmu1", "dmu2", "dsigma"]):
         strict(g[1 + k], r[2 + k], name, scale_atol=True)
+
+
+@pytest.mark.parametrize("sigma", [0.5, 0.8, 1.2, 1.6])
+@pytest.mark.parametrize("flags,opts", [
+    (0, {}), (1, {"single_dimension_kernel": 1}), (2, {"forbid_positive_dim1": 1}),
+    (4, {"unit_normalization": 0}), (8, {"square_unit_normalization": 1}),
+], ids=["default", "single_dim", "forbid_positive_dim1", "no_unit_norm", "square_unit_norm"])
+def test_kernel_compute_matches_reference_cuda(sigma, flags, opts, tmp_path):
+    """Row a1: dau_get_kernels (host, double) against the reference's DAUKernelCompute::get_kernels (its CUDA
+    kernels + cub segmented sums, fp32) for the same sigma and options: blur, the four derivative filters and the
+    rotated error filter, Kb = 7 ... 17.  fp32 sums of exp() on the reference side: 1e-4 relative, 1e-6 absolute."""
+    import dau_conv
+    ref = ref_cuda.kernels_isolated(sigma, flags, tmp_path)
+    got = dau_conv.get_kernels(dau_conv.default_settings(**opts), sigma)
+    assert ref.shape == (6,) + got[0].shape
+    for name, g, r in zip(["blur", "d_w", "d_mu1", "d_mu2", "d_sigma", "d_error"], got, ref):
+        np.testing.assert_allclose(g, r, rtol=1e-4, atol=1e-6, err_msg=name)
