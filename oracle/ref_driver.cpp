@@ -149,7 +149,8 @@ extern "C" int dau_ref_cuda_run(int N, int S, int F, int Gx, int Gy, int H, int 
                                 const float* x, const float* top_error, float* w, float* mu1, float* mu2, float* sigma,
                                 float* y, float* dx, float* dw, float* dmu1, float* dmu2, float* dsigma,
                                 int iters, float* fwd_ms, float* bwd_ms, size_t* workspace_bytes,
-                                char* errbuf, int errlen) {
+                                char* errbuf, int errlen, int opt_flags) {
+    // opt_flags: 1 use_interpolation = false, 2 single_dim_kernel, 4 forbid_positive_dim1 (TF op attrs of those names)
     cublasHandle_t cublas = nullptr;
     try {
         cudaStream_t stream;
@@ -163,7 +164,7 @@ extern "C" int dau_ref_cuda_run(int N, int S, int F, int Gx, int Gy, int H, int 
         st.mean_iteration_step = 1; st.sigma_iteration_step = 1;
         st.component_border_bound = 0.01f; st.sigma_lower_bound = 0.3f;
         st.merge_iteration_step = 0; st.merge_threshold = 1;
-        st.offsets_already_centered = true; st.use_interpolation = true;
+        st.offsets_already_centered = true; st.use_interpolation = !(opt_flags & 1);
         const std::vector<int> bottom{N, S, H, W}, top{N, F, H, W};
         const size_t P = (size_t)S * Gx * Gy * F;
         {
@@ -178,6 +179,8 @@ extern "C" int dau_ref_cuda_run(int N, int S, int F, int Gx, int Gy, int H, int 
             layer.enable_memalloc_info(false);
             layer.enable_unit_bounds_guard(false);
             layer.enable_sigma_learning(true);
+            layer.set_single_dimensional_kernel((opt_flags & 2) != 0);      // dau_conv_op.cpp:287-289
+            layer.set_forbid_positive_dim1((opt_flags & 4) != 0);
             layer.SetUp(st, &kc, &kp, &ko, bottom, units_ignore);
             std::vector<int> got = layer.Reshape(bottom, top);
             if (got != top) throw DAUException("ref_driver: unexpected top shape");
@@ -200,7 +203,8 @@ extern "C" int dau_ref_cuda_run(int N, int S, int F, int Gx, int Gy, int H, int 
                 // the whole device before each stamp so that nothing escapes the timed spans
                 CUDA_CHECK(cudaDeviceSynchronize());
                 CUDA_CHECK(cudaEventRecord(e1, stream));
-                layer.Backward_gpu(nullptr, top_error, top, true, x, dx, bottom, {true, true, true, true, false});
+                layer.Backward_gpu(nullptr, top_error, top, true, x, dx, bottom,
+                                   {true, true, !(opt_flags & 2), true, false});   // dau_conv_grad_op.cpp:291-292
                 if (mu_learning_rate_factor != 1.0f) {
                     caffe_gpu_scal<float>((int)P, mu_learning_rate_factor, dmu1, cublas);
                     caffe_gpu_scal<float>((int)P, mu_learning_rate_factor, dmu2, cublas);

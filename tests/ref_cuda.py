@@ -26,13 +26,13 @@ def lib():
         fp, i = ctypes.c_void_p, ctypes.c_int
         _lib.dau_ref_cuda_run.argtypes = [i] * 10 + [ctypes.c_float] + [fp] * 12 + [
             i, ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_size_t),
-            ctypes.c_char_p, i]
+            ctypes.c_char_p, i, i]
         _lib.dau_ref_cuda_run.restype = i
     return _lib
 
 
 def run(x, err, w, mu1, mu2, sigma, units, kernel_size=9, ignore_edge_gradients=True, units_ignore=0,
-        mu_learning_rate_factor=1.0, iters=1):
+        mu_learning_rate_factor=1.0, iters=1, opt_flags=0):
     """x, err, w, mu1, mu2, sigma: contiguous fp32 CUDA tensors (NCHW, [1,S,G,F]).  Returns
     (y, dx, dw, dmu1, dmu2, dsigma, info) as CUDA tensors; info = fwd/bwd ms per pass and workspace bytes."""
     import torch
@@ -49,7 +49,7 @@ def run(x, err, w, mu1, mu2, sigma, units, kernel_size=9, ignore_edge_gradients=
     rc = lib().dau_ref_cuda_run(N, S, F, gx, gy, H, W, kernel_size, int(ignore_edge_gradients), units_ignore,
                                 mu_learning_rate_factor,
                                 *[t.data_ptr() for t in (x, err, w, mu1, mu2, sigma, y, dx, *grads)],
-                                iters, ctypes.byref(fwd), ctypes.byref(bwd), ctypes.byref(ws), msg, 1024)
+                                iters, ctypes.byref(fwd), ctypes.byref(bwd), ctypes.byref(ws), msg, 1024, opt_flags)
     if rc != 0:
         raise RuntimeError("reference CUDA path failed: " + msg.value.decode(errors="replace"))
     torch.cuda.synchronize()
@@ -61,14 +61,15 @@ class ReferenceFault(RuntimeError):
 
 
 def run_isolated(x, err, w, mu1, mu2, sigma, units, tmp_dir, kernel_size=9, ignore_edge_gradients=True,
-                 units_ignore=0, mu_learning_rate_factor=1.0, iters=1, timeout=300):
+                 units_ignore=0, mu_learning_rate_factor=1.0, iters=1, timeout=300, opt_flags=0):
     """Same call on NumPy arrays, in a process of its own (tests/ref_cuda_worker.py): the reference build aborts
     the process on some shapes, which must not take the test session with it.  Returns NumPy arrays
-    (y, dx, dw, dmu1, dmu2, dsigma, info)."""
+    (y, dx, dw, dmu1, dmu2, dsigma, info).  opt_flags: 1 use_interpolation = false, 2 single_dim_kernel,
+    4 forbid_positive_dim1."""
     import numpy as np
     tmp_dir = str(tmp_dir)
     np.savez(os.path.join(tmp_dir, "in.npz"), x=x, err=err, w=w, mu1=mu1, mu2=mu2, sigma=sigma,
-             meta=np.array([units[0], units[1], kernel_size, int(ignore_edge_gradients), units_ignore, iters]),
+             meta=np.array([units[0], units[1], kernel_size, int(ignore_edge_gradients), units_ignore, iters, opt_flags]),
              mu_lr=np.float32(mu_learning_rate_factor))
     out = os.path.join(tmp_dir, "out.npz")
     if os.path.exists(out):

@@ -64,7 +64,7 @@ def main():
     x, err, w = z["x"], z["err"], z["w"]
     N, S, H, W = x.shape
     F = w.shape[3]
-    gx, gy, ks, edge, ignore, iters = [int(v) for v in z["meta"]]
+    gx, gy, ks, edge, ignore, iters, opt_flags = [int(v) for v in z["meta"]]
     px, pe, pw, pm1, pm2, ps = [up(z[k]) for k in ("x", "err", "w", "mu1", "mu2", "sigma")]
     py, pdx = dev(4 * N * F * H * W), dev(x.nbytes)
     pg = [dev(w.nbytes) for _ in range(4)]
@@ -72,12 +72,12 @@ def main():
     fp, i = ctypes.c_void_p, ctypes.c_int
     lib.dau_ref_cuda_run.argtypes = [i] * 10 + [ctypes.c_float] + [fp] * 12 + [
         i, ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_size_t),
-        ctypes.c_char_p, i]
+        ctypes.c_char_p, i, i]
     fwd, bwd, ws = ctypes.c_float(0), ctypes.c_float(0), ctypes.c_size_t(0)
     msg = ctypes.create_string_buffer(1024)
     rc = lib.dau_ref_cuda_run(N, S, F, gx, gy, H, W, ks, edge, ignore, float(z["mu_lr"]),
                               px, pe, pw, pm1, pm2, ps, py, pdx, *pg, iters,
-                              ctypes.byref(fwd), ctypes.byref(bwd), ctypes.byref(ws), msg, 1024)
+                              ctypes.byref(fwd), ctypes.byref(bwd), ctypes.byref(ws), msg, 1024, opt_flags)
     if rc != 0:
         sys.stderr.write("reference CUDA path refused: " + msg.value.decode(errors="replace") + "\n")
         sys.exit(3)

@@ -169,3 +169,61 @@ def test_kernel_compute_matches_reference_cuda(sigma, flags, opts, tmp_path):
     assert ref.shape == (6,) + got[0].shape
     for name, g, r in zip(["blur", "d_w", "d_mu1", "d_mu2", "d_sigma", "d_error"], got, ref):
         np.testing.assert_allclose(g, r, rtol=1e-4, atol=1e-6, err_msg=name)
+
+
+OPTION_CASES = [
+    # id, op attrs (TF names), reference driver arguments
+    # use_interpolation = false is not here: the reference's kernels refuse it unless built with
+    # -DDAU_ALLOW_INTERPOLATION_OFF ("support for non-interpolation disabled"); the oracle covers it (test_parity_gpu.py)
+    ("single_dim_kernel", dict(single_dim_kernel=True), dict(opt_flags=2)),
+    ("forbid_positive_dim1", dict(forbid_positive_dim1=True), dict(opt_flags=4)),
+    ("one_unit_ignored", dict(number_units_ignore=1), dict(units_ignore=1)),
+    ("mu_learning_rate_factor_500", dict(mu_learning_rate_factor=500.0), dict(mu_learning_rate_factor=500.0)),
+]
+
+
+@pytest.mark.parametrize("name,attrs,ref_kw", OPTION_CASES, ids=[c[0] for c in OPTION_CASES])
+def test_op_attributes_match_reference_cuda(name, attrs, ref_kw, tmp_path):
+    """The op attributes beyond the default path (row f4), each against the reference's CUDA layer driven the way
+    its TF ops drive it (dau_conv_op.cpp:283-290, dau_conv_grad_op.cpp:270-303)."""
+    import torch
+    import dau_conv
+    N, S, F, units, H, W, ks = 2, 16, 32, (1, 2), 32, 32, 9
+    G = 2
+    rng = np.random.default_rng(4711)
+    x = rng.random((N, S, H, W)).astype(np.float32)
+    err = rng.standard_normal((N, F, H, W)).astype(np.float32)
+    w = (0.1 * rng.standard_normal((1, S, G, F))).astype(np.float32)
+    mu1 = rng.uniform(-3.99, 3.99, (1, S, G, F)).astype(np.float32)
+    mu2 = rng.uniform(-3.99, 3.99, (1, S, G, F)).astype(np.float32)
+    if name == "single_dim_kernel":
+        mu2[:] = 0                      # DAUConv1d keeps mu2 at zero (dau_conv.py:716-724)
+    if name == "one_unit_ignored":
+        # The reference's NumPy model (and this repo) leave ignored units out of the forward sum
+        # (dau_conv_test.py:34), its CUDA layer only zeroes their gradients (base_dau_conv_layer.cu:346-350);
+        # the two agree because the layer initialises the dummy unit's weight to zero and never updates it
+        # (ZeroNLast, dau_conv.py:77-110) -- the state this case reproduces.
+        w[:, :, -1, :] = 0
+    sigma = np.full((1, S, G, F), 0.5, np.float32)
+    dev = torch.device("cuda:0")
+    t = [torch.from_numpy(a).to(dev) for a in (x, w, mu1, mu2, sigma)]
+    a = dict(num_output=F, number_units_x=units[0], number_units_y=units[1], kernel_size=ks, pad=4,
+             unit_testing=True, mu_learning_rate_factor=1.0)
+    a.update(attrs)
+    ours = [dau_conv.dau_conv_op(*t, **a).cpu().numpy()]
+    ours += [g.cpu().numpy() for g in dau_conv.dau_conv_grad_op(torch.from_numpy(err).to(dev), *t, **a)]
+    ref = ref_cuda.run_isolated(x, err, w, mu1, mu2, sigma, units, tmp_path, kernel_size=ks,
+                                ignore_edge_gradients=True, **ref_kw)[:6]
+    names = ["top", "bottom_error", "dw", "dmu1", "dmu2", "dsigma"]
+    # the 1-D layer's crop is two columns (dau_conv_test.py:744-751)
+    crop = 2 if name == "single_dim_kernel" else 1
+    for k, (o, r) in enumerate(zip(ours, ref)):
+        if k < 2:
+            o, r = o[..., :-crop], r[..., :-crop]
+        reference_assert_matrix(o, r, names[k])
+    strict(ours[0][..., :-1, :-crop], ref[0][..., :-1, :-crop], "top (interior)")
+    strict(ours[1][..., :-1, :-crop], ref[1][..., :-1, :-crop], "bottom_error (interior)", scale_atol=True)
+    for k in range(2, 6):
+        if name == "single_dim_kernel" and names[k] == "dmu2":
+            continue                    # not propagated by the 1-D op (dau_conv_grad_op.cpp:291-292)
+        strict(ours[k], ref[k], names[k], scale_atol=True)
