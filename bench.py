@@ -11,7 +11,13 @@ every rank runs the same per-GPU batch (weak scaling) and the [4,S,G,F] paramete
 all-reduced with NCCL inside the step; activations never cross GPUs.
 
 `--impl reference` times the CPU restatement of the reference's own CPU path (oracle/dau_cpu.c,
-all host threads) on a bounded sample of the same workload; rank 0 only.
+all host threads) on the same per-GPU batch (a bounded sample of it on a box with few cores); rank 0 only.
+
+Besides the headline line's `roofline`, `cpu_baseline` and `e2e`, the default run adds two blocks:
+  `alexnet_dau`    the AlexNet-DAU-default training step at GLOBAL batch 256 (BASELINE.json configs[2],
+                   strong scaling: 256 / N images per GPU), tools/alexnet_dau_train_step.py
+  `reference_cuda` the reference's OWN CUDA kernels compiled for sm_100a (oracle/_ref, test infrastructure)
+                   timed on the same GPU and inputs, in a process of its own (N = 1 only)
 """
 import argparse
 import ctypes as C
@@ -105,11 +111,29 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": statistics.median(sm), "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def load_cpu_reference():
+    """oracle/dau_cpu.c with ALL the host cores: torch.distributed.run exports OMP_NUM_THREADS=1 to its
+    workers when there are several per node, which would leave the OpenMP port on one core."""
+    cores = host_cores()
+    os.environ["OMP_NUM_THREADS"] = str(cores)
+    from oracle import dau_cpu
+    lib = dau_cpu.load()
+    if hasattr(lib, "dau_cpu_set_num_threads"):
+        lib.dau_cpu_set_num_threads(cores)
+    return dau_cpu, lib.dau_cpu_num_threads()
+
+
 def time_cpu_reference(cfg, n_sample, steps, warmup):
     """The reference's CPU path (restated, oracle/dau_cpu.c) on n_sample images; images/s."""
-    from oracle import dau_cpu
+    dau_cpu, cores = load_cpu_reference()
     x, e, w, mu1, mu2 = make_inputs_numpy(cfg, n_sample, 77)
-    cores = dau_cpu.load().dau_cpu_num_threads()
     times = []
     for it in range(warmup + steps):
         t0 = time.perf_counter()
@@ -122,22 +146,89 @@ def time_cpu_reference(cfg, n_sample, steps, warmup):
     return n_sample * len(times) / tot, tot / len(times) * 1e3, cores
 
 
-def run_reference(args, rank):
+def config_block(cfg, world):
+    """`config` of the JSON line; identical for both arms (the driver compares them)."""
+    N, S, F, units, H, W, ks, m = CONFIGS[cfg]
+    return {"workload": workload_name(cfg), "global_batch": N * world,
+            "parallelism": "batch-sharded dp%d, NCCL all-reduce of [4,S,G,F] parameter gradients" % world,
+            "l2": "inputs larger than L2 (x and top_error are %.0f MB each; L2 is 126 MB)" % (4.0 * N * S * H * W / 1e6)}
+
+
+def run_reference(args, rank, world):
+    """Reference arm: the reference's CPU path on the per-GPU batch, all host cores, rank 0 only.  Every step
+    is one forward + backward pass over the whole per-GPU batch when the run then fits REF_BUDGET_S
+    (calibrated on a short pass first), else over the largest 8-image multiple that does."""
     if rank != 0:
         return
+    REF_BUDGET_S = 420.0
     N = CONFIGS[args.config][0]
-    n_sample = args.cpu_sample if args.cpu_sample > 0 else max(1, N // 4)
-    value, ms, cores = time_cpu_reference(args.config, n_sample, args.steps, min(args.warmup, 1))
-    sample = "%d of the %d images of the per-GPU batch per step (all other sizes unchanged)" % (n_sample, N)
+    n_sample = args.cpu_sample
+    if n_sample <= 0:
+        n_cal = min(N, 8)
+        v_cal, _, _ = time_cpu_reference(args.config, n_cal, 1, 1)       # images/s on a short pass (also warms up)
+        passes = args.steps + args.warmup
+        n_fit = int(REF_BUDGET_S * v_cal / max(1, passes))
+        n_sample = N if n_fit >= N else max(8, n_fit // 8 * 8)
+    value, ms, cores = time_cpu_reference(args.config, n_sample, args.steps, args.warmup)
+    if n_sample == N:
+        sample = "the whole per-GPU batch (%d images) per step" % N
+    else:
+        sample = "%d of the %d images of the per-GPU batch per step (all other sizes unchanged)" % (n_sample, N)
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": ms, "higher_is_better": True,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload_name(args.config), "sample": sample},
+        "config": config_block(args.config, world),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }))
+
+
+def run_alexnet_block(rank, world, local_rank, steps, warmup):
+    """AlexNet-DAU-default training step at GLOBAL batch 256 (BASELINE.json configs[2]): strong scaling."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import torch
+    try:
+        import alexnet_dau_train_step as A
+        dev = torch.device("cuda", local_rank)
+        tr = A.Trainer("default", 256, dev, rank, world, graph=True)
+        ms, loss = tr.timed(steps, warmup)
+        out = {"metric": "alexnet_dau_train_step_images_per_sec", "value": 256.0 / (ms * 1e-3), "unit": UNIT,
+               "ms_per_step": ms, "n_gpus": world, "global_batch": 256, "scaling": "strong", "steps": steps,
+               "warmup": warmup, "loss": loss, "cuda_graph": tr._graph is not None, "graph_error": tr.graph_error,
+               "workload": tr.describe("default")}
+        del tr
+        torch.cuda.empty_cache()
+        return out
+    except Exception as ex:                                    # the headline line must not die with this block
+        return {"error": "%s: %s" % (type(ex).__name__, str(ex)[:300])}
+
+
+def run_reference_cuda_block(cfg, ours_ms):
+    """The reference's own CUDA kernels (oracle/_ref/libdau_ref_cuda.so, sm_100a build of the sources under
+    /root/reference) on this GPU and these inputs, in a process of its own (it aborts on some shapes)."""
+    so = os.path.join(ROOT, "oracle", "_ref", "libdau_ref_cuda.so")
+    if not os.path.exists(so):
+        return {"unavailable": "oracle/_ref/libdau_ref_cuda.so not built"}
+    N = CONFIGS[cfg][0]
+    out = os.path.join(ROOT, "gpurun_out", "_refcuda_bench_%d.json" % os.getpid())
+    os.makedirs(os.path.dirname(out), exist_ok=True)
+    try:
+        r = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "ref_cuda_worker.py"), "--bench", cfg, str(N),
+                            "6", out], capture_output=True, text=True, timeout=300)
+        if r.returncode != 0 or not os.path.exists(out):
+            return {"error": "exit %d: %s" % (r.returncode, (r.stderr or "").strip()[-300:])}
+        d = json.load(open(out))
+        os.remove(out)
+    except Exception as ex:
+        return {"error": "%s: %s" % (type(ex).__name__, str(ex)[:300])}
+    ref_ms = d["fwd_ms"] + d["bwd_ms"]
+    return {"step_ms": ref_ms, "fwd_ms": d["fwd_ms"], "bwd_ms": d["bwd_ms"], "images_per_s": N / ref_ms * 1e3,
+            "speedup_of_this_repo": ref_ms / ours_ms, "workspace_bytes": d["workspace_bytes"],
+            "what": "BaseDAUConvLayer<float>::Forward_gpu + Backward_gpu of the reference (include/dau_conv/dau_conv_impl/"
+                    "dau_conv_forward_core.hpp:804-1605, dau_conv_backward_core.hpp:1017-1820) compiled for sm_100a by "
+                    "oracle/Makefile.refcuda, layer object built once, %d timed passes, CUDA events" % d["iters"]}
 
 
 def run_ours(args, rank, world, local_rank):
@@ -145,6 +236,7 @@ def run_ours(args, rank, world, local_rank):
     import torch.distributed as dist
     import dau_conv
     from dau_conv import _lib
+    from dau_conv.distributed import GradBucket
 
     dev = torch.device("cuda", local_rank)
     torch.cuda.set_device(dev)
@@ -165,15 +257,14 @@ def run_ours(args, rank, world, local_rank):
                             kernel_size=ks, pad=(ks - 1) // 2)
     h.set_sigma_hint(0.5)                                        # sigma is fixed (dau_sigma_trainable=False)
     y = torch.empty((N, F, H, W), device=dev)
-    flat = torch.zeros((4, 1, S, G, F), device=dev)              # one buffer: w, mu1, mu2, sigma grads
-    grads = [flat[k] for k in range(4)]
+    bucket = GradBucket((1, S, G, F), dev)                       # one flat buffer: w, mu1, mu2, sigma grads
+    flat, grads = bucket.flat, bucket.views
 
     def step():
         h.forward(x, w, mu1, mu2, sigma, out=y)
-        flat.zero_()                                             # the op pre-zeroes (grad_op.cpp:202-205)
+        bucket.zero_()                                           # the op pre-zeroes (grad_op.cpp:202-205)
         out = h.backward(x, e, w, mu1, mu2, sigma, grads=grads)
-        if world > 1:
-            dist.all_reduce(flat)                                # only the parameter gradients cross GPUs
+        bucket.all_reduce()                                      # only the parameter gradients cross GPUs (no-op at N=1)
         return out
 
     def sync_all():
@@ -222,11 +313,15 @@ def run_ours(args, rank, world, local_rank):
     flops = {"gather_forward": 8.0 * U, "gather_backprop": 8.0 * U, "grad_units": 16.0 * U}
     top = max(flops, key=lambda k: acc.get(k, 0.0))
     achieved = flops[top] / (acc[top] * 1e-3) / 1e12
-    traffic = None
+    # HBM bytes the dominant kernel really moved per launch: an ncu --set full capture of an earlier run
+    # of the same command (profiles/traffic.json names the capture and the build it was made from)
+    traffic, traffic_source = None, None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tpath):
         try:
-            traffic = json.load(open(tpath)).get(args.config, {}).get(top)
+            tj = json.load(open(tpath))
+            traffic = tj.get(args.config, {}).get(top)
+            traffic_source = tj.get("_source") if traffic is not None else None
         except Exception:
             traffic = None
     hbm_peak = None
@@ -236,14 +331,21 @@ def run_ours(args, rank, world, local_rank):
         hbm_peak = 6650.0
     min_bytes = 4.0 * N * H * W * (3 * S + 2 * F) + 4.0 * 8 * S * G * F
     kernel_ms_sum = sum(acc.values())
+    props = torch.cuda.get_device_properties(dev)
+    clk = sampler.summary() if sampler else {}
+    sm_max_mhz = clk.get("sm_max_mhz") or 1965.0
+    nominal_peak = props.multi_processor_count * 128 * 2 * sm_max_mhz * 1e6 / 1e12     # SMs x 128 FMA lanes x 2 flop x clock
     roofline = {
         "bound": "fp32_fma", "kernel": top, "achieved": achieved, "peak": fma_peak, "unit": "TFLOP/s",
-        "frac": achieved / fma_peak, "traffic": traffic,
-        "peak_source": "FP32 FFMA peak measured in this run on this GPU (MEASURED_PEAKS.json has no fp32 figure); "
-                       "the op is a gather-accumulate on CUDA cores, neither HBM- nor tensor-bound",
+        "frac": achieved / fma_peak, "traffic": traffic, "traffic_source": traffic_source,
+        "peak_nominal": nominal_peak, "frac_nominal": achieved / nominal_peak,
+        "peak_source": "`peak`: FP32 FFMA rate measured in this run on this GPU (register-resident FMA chains on every "
+                       "SM; MEASURED_PEAKS.json has no fp32 figure); `peak_nominal`: SMs x 128 lanes x 2 flop x max SM "
+                       "clock; the op is a gather-accumulate on CUDA cores, neither HBM- nor tensor-bound",
         "algorithmic_flops_per_launch": flops[top],
         "kernel_ms": {k: round(v, 4) for k, v in acc.items()},
         "step_fraction_of_fma_peak": 32.0 * U / (kernel_ms_sum * 1e-3) / 1e12 / fma_peak,
+        "step_fraction_of_nominal_peak": 32.0 * U / (kernel_ms_sum * 1e-3) / 1e12 / nominal_peak,
         "hbm": {"algorithmic_bytes_per_step": min_bytes, "achieved_gbs": min_bytes / (kernel_ms_sum * 1e-3) / 1e9,
                 "peak_gbs": hbm_peak, "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)"},
     }
@@ -259,11 +361,10 @@ def run_ours(args, rank, world, local_rank):
 
     def e2e_step():
         # the public host-buffer call: chunked H2D -> fwd+bwd -> D2H, copies overlapped with kernels
-        flat.zero_()
+        bucket.zero_()
         h.train_step_host(xp, ep, w, mu1, mu2, sigma, 0.5, y_host=yp, dx_host=dxp, grads=grads,
                           chunk_images=e2e_chunk)
-        if world > 1:
-            dist.all_reduce(flat)
+        bucket.all_reduce()
         gp.copy_(flat, non_blocking=True)
 
     e2e_step()
@@ -280,8 +381,15 @@ def run_ours(args, rank, world, local_rank):
     h2d = xh.nbytes + eh.nbytes
     d2h = yp.numel() * 4 + dxp.numel() * 4 + gp.numel() * 4
 
+    # ---- secondary blocks (after, and outside, every timed region of the headline metric) -----------------
+    alexnet = None
+    if args.config == "c2" and not args.no_alexnet:
+        alexnet = run_alexnet_block(rank, world, local_rank, args.alexnet_steps, 3)
     if rank != 0:
         return
+    reference_cuda = None
+    if world == 1 and not args.no_reference_cuda:
+        reference_cuda = run_reference_cuda_block(args.config, ms_step)
     cpu_baseline = None
     if world == 1 and not args.no_cpu_baseline:
         n_cpu = args.cpu_sample if args.cpu_sample > 0 else N
@@ -293,15 +401,13 @@ def run_ours(args, rank, world, local_rank):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload_name(args.config), "global_batch": N * world,
-                   "parallelism": "batch-sharded dp%d, NCCL all-reduce of [4,S,G,F] parameter gradients" % world,
-                   "l2": "inputs larger than L2 (x and top_error are %.0f MB each; L2 is 126 MB)" % (xh.nbytes / 1e6)},
-        "roofline": roofline, "cpu_baseline": cpu_baseline,
+        "config": config_block(args.config, world),
+        "roofline": roofline, "cpu_baseline": cpu_baseline, "alexnet_dau": alexnet, "reference_cuda": reference_cuda,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "steps": e2e_steps, "max_chunk_images": e2e_chunk,
                 "what": "dau_train_step_host: pinned host x, top_error -> device; fwd+bwd; y, dL/dx and the "
                         "4 parameter gradients -> pinned host; copies overlapped with the kernels chunk by chunk"},
-        "gpu_launches": launches, "clocks": sampler.summary() if sampler else None,
+        "gpu_launches": launches, "clocks": clk if sampler else None,
     }))
 
 
@@ -316,6 +422,9 @@ def main():
                     help="images per CPU pass (0: the whole per-GPU batch for the cpu_baseline leg, about 10-15 s "
                          "on C2; a quarter of it per step for --impl reference)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-alexnet", action="store_true", help="skip the AlexNet-DAU strong-scaling block")
+    ap.add_argument("--alexnet-steps", type=int, default=10)
+    ap.add_argument("--no-reference-cuda", action="store_true", help="skip the reference-CUDA comparison block")
     ap.add_argument("--e2e-chunk", type=int, default=0,
                     help="largest chunk of the host-buffer step in images (0: half the per-GPU batch); the library "
                          "searches the chunk schedule under this cap")
@@ -324,7 +433,7 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
-        run_reference(args, rank)
+        run_reference(args, rank, world)
         return
     if world > 1:
         import torch

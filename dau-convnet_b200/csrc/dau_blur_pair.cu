@@ -320,11 +320,11 @@ void launch_c(const float* in, float* out, PairBlurArgs& a, int pairs_times_c, c
     const bool use_tma = ident && a.crop == 0 && (a.W & 3) == 0 && (reinterpret_cast<size_t>(in) & 15) == 0 &&
                          (reinterpret_cast<size_t>(a.mask) & 15) == 0;
     const size_t smem = G::SMEM + (a.mask ? G::SMEM_MASK : 0);
-    static bool attr_set = false;
-    if (!attr_set) {
+    static PerDeviceOnce once;                 // the attribute is per (kernel, device)
+    if (once.need()) {
         DAU_CUDA_CHECK(cudaFuncSetAttribute(blur_pair_kernel<MODE, C, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(G::SMEM + G::SMEM_MASK)));
         DAU_CUDA_CHECK(cudaFuncSetAttribute(blur_pair_kernel<MODE, C, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(G::SMEM + G::SMEM_MASK)));
-        attr_set = true;
+        once.done();
     }
     CUtensorMap map, mmap;
     memset(&map, 0, sizeof(map));

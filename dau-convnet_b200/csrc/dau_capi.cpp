@@ -180,7 +180,7 @@ dau_status_t dau_forward_host(dau_handle_t* h, int N, int S, int H, int W, const
     if (!h) return fail(DAU_ERR_INVALID_ARGUMENT, "dau_forward_host: NULL handle");
     return guarded([&] {
         DAUConvLayerB200* l = h->layer;
-        DAU_CUDA_CHECK(cudaSetDevice(l->device()));
+        dau::DeviceGuard guard(l->device());
         size_t fws = 0, bws = 0;
         l->Reshape(N, S, H, W, &fws, &bws);
         const size_t nin = (size_t)N * S * H * W, nout = (size_t)N * l->F() * l->H_out() * l->W_out();
@@ -203,7 +203,7 @@ dau_status_t dau_backward_host(dau_handle_t* h, int N, int S, int H, int W, cons
     if (!h) return fail(DAU_ERR_INVALID_ARGUMENT, "dau_backward_host: NULL handle");
     return guarded([&] {
         DAUConvLayerB200* l = h->layer;
-        DAU_CUDA_CHECK(cudaSetDevice(l->device()));
+        dau::DeviceGuard guard(l->device());
         size_t fws = 0, bws = 0;
         l->Reshape(N, S, H, W, &fws, &bws);
         const size_t nin = (size_t)N * S * H * W, nout = (size_t)N * l->F() * l->H_out() * l->W_out();
@@ -257,9 +257,21 @@ int dau_mosaic_to_real(const int* q, int N, int nv, int vy, int vx, int* n, int*
     return dau::mosaic_to_real(m, nv, vy, vx, n, y, x) ? 1 : 0;
 }
 
+int dau_edge_mask_rule(int extent) { return DAUConvLayerB200::edge_mask_rule(extent) ? 1 : 0; }
+
+dau_status_t dau_debug_unit_tables(dau_handle_t* h, const float* w, const float* mu1, const float* mu2,
+                                   void* fwd_out, void* bwd_out, void* grad_out, int* halos4, void* stream) {
+    if (!h) return fail(DAU_ERR_INVALID_ARGUMENT, "dau_debug_unit_tables: NULL handle");
+    return guarded([&] {
+        h->layer->debug_unit_tables(w, mu1, mu2, static_cast<dau::UnitRec*>(fwd_out),
+                                    static_cast<dau::UnitRec*>(bwd_out), static_cast<dau::UnitRec*>(grad_out),
+                                    halos4, (cudaStream_t)stream);
+    });
+}
+
 dau_status_t dau_measure_fma_peak(int device, int iters, double* tflops_out, double* ms_out) {
     return guarded([&] {
-        DAU_CUDA_CHECK(cudaSetDevice(device));
+        dau::DeviceGuard guard(device);
         cudaDeviceProp prop;
         DAU_CUDA_CHECK(cudaGetDeviceProperties(&prop, device));
         const int blocks = prop.multiProcessorCount * 8;

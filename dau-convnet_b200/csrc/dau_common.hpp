@@ -2,6 +2,7 @@
 // beyond cudaStream_t so plain C++ translation units can include it).
 #pragma once
 #include <cuda_runtime.h>
+#include <atomic>
 #include <cstddef>
 #include <cstdint>
 #include <stdexcept>
@@ -24,6 +25,52 @@ struct DAUException : public std::runtime_error {
     do { cudaError_t e__ = (expr); if (e__ != cudaSuccess) throw ::dau::DAUException(2,     \
             std::string("CUDA error: ") + cudaGetErrorString(e__) + " in " #expr " at "     \
             __FILE__ ":" + std::to_string(__LINE__)); } while (0)
+
+// Kernel attributes (cudaFuncAttributeMaxDynamicSharedMemorySize) belong to a (kernel, DEVICE) pair:
+// one of these per kernel instantiation remembers on which devices the attribute has been set, so a
+// process that drives handles on several GPUs (the reference's model: one layer object per device,
+// base_dau_conv_layer.hpp:177-225) opts in on each of them.  Lock-free; two host threads may both set
+// the attribute the first time, which is harmless.
+struct PerDeviceOnce {
+    std::atomic<unsigned long long> mask[4] = {};       // up to 256 device ordinals
+    int dev = 0;
+    bool need() {
+        if (cudaGetDevice(&dev) != cudaSuccess) return true;
+        if (dev < 0 || dev >= 256) return true;
+        return !((mask[dev >> 6].load(std::memory_order_acquire) >> (dev & 63)) & 1ull);
+    }
+    void done() {
+        if (dev >= 0 && dev < 256) mask[dev >> 6].fetch_or(1ull << (dev & 63), std::memory_order_release);
+    }
+};
+
+// Restores the calling thread's current device when a C-ABI entry point returns: the library switches
+// to the handle's device for its launches and must not leave the caller (torch, a Caffe-style host)
+// on another GPU than it was on.
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int device) {
+        cudaGetDevice(&prev);
+        if (device >= 0 && device != prev) {
+            cudaError_t e = cudaSetDevice(device);
+            if (e != cudaSuccess) throw DAUException(2, std::string("CUDA error: ") + cudaGetErrorString(e) + " in cudaSetDevice");
+        } else {
+            prev = -1;
+        }
+    }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+    DeviceGuard(const DeviceGuard&) = delete;
+    DeviceGuard& operator=(const DeviceGuard&) = delete;
+};
+
+// Development switches (skip the TMA loads / the math inside the hot kernels to time their parts) exist
+// only in builds made with -DDAU_DEV_SWITCHES; the shipped library has no environment variable that
+// changes results.
+#ifdef DAU_DEV_SWITCHES
+#define DAU_DEV_BITS(x) (x)
+#else
+#define DAU_DEV_BITS(x) 0
+#endif
 
 constexpr int kMaxBlurTaps = 17;   // reference limit: Kb <= 17, sigma <= 1.6 (convolve.cu:40,230-246)
 

@@ -67,7 +67,7 @@ struct TGatherParams {
     int N, Cin, Cout, G, H, W;
     int tiles_x, nstage;
     int stage_bytes;       // tile + records, multiple of 128
-    int debug;
+    int debug;             // development switches, only with -DDAU_DEV_SWITCHES (dau_common.hpp)
     int relu;              // epilogue: store max(0, y + bias)  
     int gx, gy;            // items are numbered (pair * gy + channel group) * gx + tile
     int full_items, split_k;   // items >= full_items are cut into split_k parts of the input-channel loop
@@ -185,15 +185,15 @@ dau_gather_tma_kernel(const __grid_constant__ CUtensorMap in_map, const TGatherP
         // ---- producer warpgroup: one lane streams the input channels ----------------------------
         asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;\n" ::"n"(PROD_REGS));
         if (warp == -4 && lane == 0) {
-            if (!(p.debug & 1)) prefetch_map(&in_map);
-            const uint32_t tx_bytes = ((p.debug & 2) ? 0 : GEO::TILE_BYTES) + ((p.debug & 4) ? 0 : nrec * (uint32_t)sizeof(UnitRec));
+            if (!(DAU_DEV_BITS(p.debug) & 1)) prefetch_map(&in_map);
+            const uint32_t tx_bytes = ((DAU_DEV_BITS(p.debug) & 2) ? 0 : GEO::TILE_BYTES) + ((DAU_DEV_BITS(p.debug) & 4) ? 0 : nrec * (uint32_t)sizeof(UnitRec));
             for (int ci = ci_begin; ci < ci_end; ++ci) {
                 const int st = (ci - ci_begin) % nstage, use = (ci - ci_begin) / nstage;
                 if (use > 0) mbar_wait_backoff(&empty_bar[st], (use - 1) & 1);
                 unsigned char* dst = smem_raw + (size_t)st * p.stage_bytes;
                 mbar_arrive_expect_tx(&full_bar[st], tx_bytes);
-                if (!(p.debug & 2)) tensor4_g2s(dst, &in_map, 2 * ((x0 - GEO::HX) / 4), 0, y0 - GEO::HY, np * p.Cin + ci, &full_bar[st]);
-                if (!(p.debug & 4)) bulk_g2s(dst + GEO::TILE_BYTES, p.table + ((size_t)ci * p.Cout + co0) * p.G,
+                if (!(DAU_DEV_BITS(p.debug) & 2)) tensor4_g2s(dst, &in_map, 2 * ((x0 - GEO::HX) / 4), 0, y0 - GEO::HY, np * p.Cin + ci, &full_bar[st]);
+                if (!(DAU_DEV_BITS(p.debug) & 4)) bulk_g2s(dst + GEO::TILE_BYTES, p.table + ((size_t)ci * p.Cout + co0) * p.G,
                          nrec * (uint32_t)sizeof(UnitRec), &full_bar[st]);
             }
         }
@@ -307,11 +307,11 @@ constexpr int kHalos[4] = {4, 8, 16, 32};
 
 template <int HALO, int R>
 void launch_t(const GatherPlan& plan, const CUtensorMap& map, const TGatherParams& p, cudaStream_t stream) {
-    static bool attr_set = false;
-    if (!attr_set) {
+    static PerDeviceOnce once;                 // the attribute is per (kernel, device)
+    if (once.need()) {
         DAU_CUDA_CHECK(cudaFuncSetAttribute(dau_gather_tma_kernel<HALO, R>,
                                             cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
-        attr_set = true;
+        once.done();
     }
     const long long items = (long long)plan.grid_x * plan.grid_y * plan.grid_z;
     const long long ctas = plan.full_items + (items - plan.full_items) * plan.split_k;
@@ -420,7 +420,10 @@ void launch_gather_tma(const GatherPlan& plan, const float* in_paired, const Uni
     p.gx = plan.grid_x; p.gy = plan.grid_y; p.full_items = plan.full_items; p.split_k = plan.split_k;
     p.part = reinterpret_cast<float2*>(part_buf);
     DAU_CHECK(plan.part_bytes == 0 || part_buf != nullptr, 3, "gather plan splits its tail but no partial buffer was given");
+    p.debug = 0;
+#ifdef DAU_DEV_SWITCHES
     p.debug = getenv("DAU_DEBUG") ? atoi(getenv("DAU_DEBUG")) : 0;
+#endif
 #define DAU_LAUNCH(HALO)                                                     \
     switch (plan.tile_h / LY) {                                              \
         case 16: launch_t<HALO, 16>(plan, map, p, stream); break;            \

@@ -144,8 +144,8 @@ dau_grad_tma_kernel(const __grid_constant__ CUtensorMap err_map, const TGradPara
             prefetch_map(&err_map);
             // Error tiles go through a 2-stage ring.  Xk needs ONE buffer only: the consumers move it
             // to registers at the start of an item, so the next item's 64 KB copy overlaps the math.
-            const uint32_t tx_e = (p.debug & 2) ? 0 : nfeat * GEO::FEAT_BYTES;
-            const uint32_t tx_x = (p.debug & 4) ? 0 : nsv * XK_WARP_BYTES;
+            const uint32_t tx_e = (DAU_DEV_BITS(p.debug) & 2) ? 0 : nfeat * GEO::FEAT_BYTES;
+            const uint32_t tx_x = (DAU_DEV_BITS(p.debug) & 4) ? 0 : nsv * XK_WARP_BYTES;
             unsigned char* xdst = smem_raw + 2 * (size_t)p.stage_bytes;
             for (int item = item_begin; item < item_end; ++item) {
                 const int k = item - item_begin, st = k & 1, use = k >> 1;
@@ -153,12 +153,12 @@ dau_grad_tma_kernel(const __grid_constant__ CUtensorMap err_map, const TGradPara
                 const int tyi = t / p.tiles_x, txi = t - tyi * p.tiles_x;
                 if (k > 0) mbar_wait_backoff(&xempty_bar, (k - 1) & 1);
                 mbar_arrive_expect_tx(&xfull_bar, tx_x);
-                if (!(p.debug & 4)) bulk_g2s(xdst, p.xs + ((size_t)item * p.S + s0) * (XK_WARP_BYTES / 4),
+                if (!(DAU_DEV_BITS(p.debug) & 4)) bulk_g2s(xdst, p.xs + ((size_t)item * p.S + s0) * (XK_WARP_BYTES / 4),
                                              nsv * XK_WARP_BYTES, &xfull_bar);
                 if (use > 0) mbar_wait_backoff(&empty_bar[st], (use - 1) & 1);
                 unsigned char* dst = smem_raw + (size_t)st * p.stage_bytes;
                 mbar_arrive_expect_tx(&full_bar[st], tx_e);
-                for (int fi = 0; fi < nfeat && !(p.debug & 2); ++fi)
+                for (int fi = 0; fi < nfeat && !(DAU_DEV_BITS(p.debug) & 2); ++fi)
                     tensor4_g2s(dst + fi * p.feat_bytes_al, &err_map, txi * TW - GEO::HX, 0,
                                 tyi * TH - GEO::HY, n * F + f0 + fi, &full_bar[st]);
             }
@@ -195,7 +195,7 @@ dau_grad_tma_kernel(const __grid_constant__ CUtensorMap err_map, const TGradPara
         if (lane == 0) mbar_arrive(&xempty_bar);           // the buffer may be refilled while we compute
         mbar_wait(&full_bar[st], use & 1);
         const unsigned char* sbase = smem_raw + (size_t)st * p.stage_bytes;
-        if (s_valid && !(p.debug & 8)) {
+        if (s_valid && !(DAU_DEV_BITS(p.debug) & 8)) {
             const float2* tb = reinterpret_cast<const float2*>(sbase) + lane;
 #pragma unroll
             for (int u = 0; u < UPW; ++u) {
@@ -264,11 +264,11 @@ constexpr int kHalos[4] = {4, 8, 16, 32};
 
 template <int HALO>
 void launch_t(const GradPlan& plan, const CUtensorMap& map, const TGradParams& p, cudaStream_t stream) {
-    static bool attr_set = false;
-    if (!attr_set) {
+    static PerDeviceOnce once;                 // the attribute is per (kernel, device)
+    if (once.need()) {
         DAU_CUDA_CHECK(cudaFuncSetAttribute(dau_grad_tma_kernel<HALO>,
                                             cudaFuncAttributeMaxDynamicSharedMemorySize, 221 * 1024));
-        attr_set = true;
+        once.done();
     }
     dim3 grid(plan.grid_x, plan.grid_y, plan.grid_z);
     dau_grad_tma_kernel<HALO><<<grid, NTHREADS, plan.smem_bytes, stream>>>(map, p);
@@ -355,7 +355,10 @@ void launch_grad_tma(const GradPlan& plan, const float* xk_strips, const float* 
     p.items_per_split = (p.items + plan.n_splits - 1) / plan.n_splits;
     p.feat_bytes_al = plan.feat_stride * 4;
     p.stage_bytes = plan.feats_per_cta * plan.feat_stride * 4;
+    p.debug = 0;
+#ifdef DAU_DEV_SWITCHES
     p.debug = getenv("DAU_DEBUG_GRAD") ? atoi(getenv("DAU_DEBUG_GRAD")) : 0;
+#endif
     switch (plan.variant) {
         case 0: launch_t<4>(plan, map, p, stream); break;
         case 1: launch_t<8>(plan, map, p, stream); break;

@@ -23,7 +23,7 @@
 namespace dau {
 
 HostPipeline::HostPipeline(const dau_settings_t& st, int device) : st_(st), device_(device) {
-    DAU_CUDA_CHECK(cudaSetDevice(device));
+    DeviceGuard guard(device);
     DAU_CUDA_CHECK(cudaStreamCreateWithFlags(&s_in_, cudaStreamNonBlocking));
     DAU_CUDA_CHECK(cudaStreamCreateWithFlags(&s_comp_, cudaStreamNonBlocking));
     DAU_CUDA_CHECK(cudaStreamCreateWithFlags(&s_out_, cudaStreamNonBlocking));
@@ -38,6 +38,8 @@ HostPipeline::HostPipeline(const dau_settings_t& st, int device) : st_(st), devi
 }
 
 HostPipeline::~HostPipeline() {
+    int prev = -1;
+    cudaGetDevice(&prev);
     cudaSetDevice(device_);
     cudaDeviceSynchronize();
     for (auto& kv : layers_) delete kv.second;
@@ -48,6 +50,7 @@ HostPipeline::~HostPipeline() {
     }
     cudaEventDestroy(fork_);
     cudaStreamDestroy(s_in_); cudaStreamDestroy(s_comp_); cudaStreamDestroy(s_out_);
+    if (prev >= 0 && prev != device_) cudaSetDevice(prev);
 }
 
 DAUConvLayerB200* HostPipeline::layer_for(int n, int S, int H, int W, float sigma_hint, size_t* fws, size_t* bws) {
@@ -167,7 +170,7 @@ void HostPipeline::step(int N, int S, int H, int W, int chunk, float sigma_hint,
                         float* dx, float* dw, float* dmu1, float* dmu2, float* dsigma, cudaStream_t stream) {
     DAU_CHECK(N > 0 && chunk > 0, 1, "batch and chunk must be positive");
     DAU_CHECK(x && top_error && w && mu1 && mu2 && dw && dmu1 && dmu2 && dsigma, 1, "NULL tensor pointer");
-    DAU_CUDA_CHECK(cudaSetDevice(device_));
+    DeviceGuard guard(device_);
     chunk = std::min(chunk, N);
     const int F = st_.num_output;
     const int crop = (st_.kernel_size - 1) / 2 - st_.pad;             // top is [N, F, H-2crop, W-2crop]

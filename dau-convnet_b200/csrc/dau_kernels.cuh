@@ -148,8 +148,11 @@ struct GradFinalizeArgs {
 };
 void launch_grad_finalize(const GradFinalizeArgs& a, cudaStream_t stream);
 
-// bias gradient: dbias[f] += sum_{n,y,x} err[n,f,y,x]
-void launch_bias_grad(const float* err, const float* act, float* dbias, int N, int F, int HW, cudaStream_t stream);
+// bias gradient: dbias[f] += sum_{n,y,x} err[n,f,y,x]; `partial` = bias_grad_partial_floats(F) floats of
+// workspace (two-stage deterministic sum, no atomics)
+size_t bias_grad_partial_floats(int F);
+void launch_bias_grad(const float* err, const float* act, float* dbias, float* partial, int N, int F, int HW,
+                      cudaStream_t stream);
 
 // FP32 FMA peak probe (register-resident FFMA chains on every SM)
 void launch_fma_probe(float* sink, int iters, int blocks, cudaStream_t stream);

@@ -84,7 +84,7 @@ DAUConvLayerB200::DAUConvLayerB200(const dau_settings_t& s, int device) : st_(s)
     F_ = s.num_output;
     max_off_ = s.kernel_size / 2;
     if (device_ < 0) DAU_CUDA_CHECK(cudaGetDevice(&device_));   // negative = the caller's current device
-    DAU_CUDA_CHECK(cudaSetDevice(device_));
+    DeviceGuard guard(device_);
     cudaDeviceProp prop;
     DAU_CUDA_CHECK(cudaGetDeviceProperties(&prop, device_));
     DAU_CHECK(prop.major >= 10, 4, "this library is built for sm_100a (B200) only");
@@ -96,7 +96,7 @@ DAUConvLayerB200::DAUConvLayerB200(const dau_settings_t& s, int device) : st_(s)
 
 bool DAUConvLayerB200::take_nan_flag(cudaStream_t stream) {
     int v = 0;
-    DAU_CUDA_CHECK(cudaSetDevice(device_));
+    DeviceGuard guard(device_);
     DAU_CUDA_CHECK(cudaMemcpyAsync(&v, nan_flag_, sizeof(int), cudaMemcpyDeviceToHost, stream));
     DAU_CUDA_CHECK(cudaMemsetAsync(nan_flag_, 0, sizeof(int), stream));
     DAU_CUDA_CHECK(cudaStreamSynchronize(stream));
@@ -149,6 +149,7 @@ void DAUConvLayerB200::Reshape(int N, int S, int H, int W, size_t* fwd_ws, size_
     off_bwd_gtable_ = o;  o = align_up(o + units * sizeof(UnitRec));
     off_bwd_partial_ = o; o = align_up(o + grad_plan_.partial_floats * sizeof(float));
     off_bwd_part_ = o;    o = align_up(o + bwd_plan_.part_bytes);
+    off_bwd_bias_ = o;    o = align_up(o + (st_.bias_term ? bias_grad_partial_floats(F_) * sizeof(float) : 0));
     bwd_ws_ = o;
     shaped_ = true;
     if (fwd_ws) *fwd_ws = fwd_ws_;
@@ -175,6 +176,33 @@ const BlurFactors& DAUConvLayerB200::factors_for(const float* sigma_dev, cudaStr
         cached_sigma_ = sigma;
     }
     return factors_;
+}
+
+bool DAUConvLayerB200::edge_mask_rule(int extent) { return edge_rule(extent); }
+
+void DAUConvLayerB200::debug_unit_tables(const float* w, const float* mu1, const float* mu2, UnitRec* fwd,
+                                         UnitRec* bwd, UnitRec* grad, int* halos4, cudaStream_t stream) {
+    DAU_CHECK(shaped_, 3, "dau_debug_unit_tables called before dau_reshape");
+    DAU_CHECK(w && mu1 && mu2, 1, "NULL tensor pointer");
+    DeviceGuard guard(device_);
+    UnitPrepArgs ua;
+    ua.w = w; ua.mu1 = mu1; ua.mu2 = mu2; ua.S = S_; ua.G = G_; ua.F = F_;
+    ua.g_active = G_ - st_.number_units_ignore;
+    ua.max_off = eff_off_; ua.use_interpolation = st_.use_interpolation; ua.mu_center = mu_center();
+    // exactly the two launches of Forward_gpu / Backward_gpu
+    if (fwd) {
+        ua.halo_x = fwd_plan_.halo_x; ua.halo_y = fwd_plan_.halo_y; ua.ghalo_x = ua.halo_x; ua.ghalo_y = ua.halo_y;
+        launch_unit_prep(ua, fwd, nullptr, nullptr, nan_flag_, stream);
+    }
+    if (bwd || grad) {
+        ua.halo_x = bwd_plan_.halo_x; ua.halo_y = bwd_plan_.halo_y;
+        ua.ghalo_x = grad_plan_.halo_x; ua.ghalo_y = grad_plan_.halo_y;
+        launch_unit_prep(ua, nullptr, bwd, grad, nan_flag_, stream);
+    }
+    if (halos4) {
+        halos4[0] = fwd_plan_.halo_x; halos4[1] = fwd_plan_.halo_y;
+        halos4[2] = grad_plan_.halo_x; halos4[3] = grad_plan_.halo_y;
+    }
 }
 
 void DAUConvLayerB200::set_activation(int act) {
@@ -230,7 +258,7 @@ void DAUConvLayerB200::Forward_gpu(const float* bottom, float* w, float* mu1, fl
     DAU_CHECK(bottom && w && mu1 && mu2 && top, 1, "NULL tensor pointer");
     DAU_CHECK(ws != nullptr && ws_bytes >= fwd_ws_, 3, "forward workspace missing or too small");
     DAU_CHECK(!st_.bias_term || bias, 1, "bias_term is set but bias pointer is NULL");
-    DAU_CUDA_CHECK(cudaSetDevice(device_));
+    DeviceGuard guard(device_);
     if (timing_) for (auto& sl : slots_[0]) sl.used = false;
     char* base = static_cast<char*>(ws);
     float* xb = reinterpret_cast<float*>(base + off_fwd_blur_);
@@ -279,7 +307,7 @@ void DAUConvLayerB200::Backward_gpu(const float* bottom, const float* top_error,
     // ReLU backward fused into every load of the top error (row f3): error := 0 where top_data <= 0
     const float* act = activation_ == DAU_ACT_RELU ? top_data : nullptr;
     DAU_CHECK(ws != nullptr && ws_bytes >= bwd_ws_, 3, "backward workspace missing or too small");
-    DAU_CUDA_CHECK(cudaSetDevice(device_));
+    DeviceGuard guard(device_);
     if (timing_) for (auto& sl : slots_[1]) sl.used = false;
     char* base = static_cast<char*>(ws);
     float* xk = reinterpret_cast<float*>(base + off_bwd_xk_);
@@ -351,7 +379,9 @@ void DAUConvLayerB200::Backward_gpu(const float* bottom, const float* top_error,
     }
     if ((flags & DAU_GRAD_BIAS) && st_.bias_term && dbias) {
         tic(1, 6, stream);
-        launch_bias_grad(top_error, act, dbias, N_, F_, H_out() * W_out(), stream);
+        launch_bias_grad(top_error, act, dbias, reinterpret_cast<float*>(base + off_bwd_bias_), N_, F_,
+                         H_out() * W_out(), stream);
+        ++launches_;                                      // the second stage
         toc(1, 6, stream);
     }
 }

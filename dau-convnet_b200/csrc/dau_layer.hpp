@@ -52,6 +52,13 @@ public:
     // treated as w = 0); blocks on `stream`.  The TF op fails the call instead (dau_conv_op.cpp:258-262)
     // because it reads max|mu| back on every call anyway; here the read is the caller's choice.
     bool take_nan_flag(cudaStream_t stream);
+    // Test hook (dau_debug_unit_tables): the three unit tables the kernels would read for these parameters,
+    // written to caller-provided device buffers of S*G*F records (any may be NULL); halos4 = {gather
+    // halo x, y, gradient halo x, y} are the amounts added to the integer offsets in the records.
+    void debug_unit_tables(const float* w, const float* mu1, const float* mu2, UnitRec* fwd, UnitRec* bwd,
+                           UnitRec* grad, int* halos4, cudaStream_t stream);
+    // ignore_edge_gradients rule for one output extent (dau_conv_test.py:110-136)
+    static bool edge_mask_rule(int extent);
     void enable_timing(bool e);
     int  get_timing(int which, float* ms, int cap);
     static const char* timing_name(int which, int idx);
@@ -88,7 +95,7 @@ private:
     // workspace carving (byte offsets)
     size_t off_fwd_blur_ = 0, off_fwd_table_ = 0, off_fwd_part_ = 0, off_bwd_part_ = 0;
     size_t off_bwd_xk_ = 0, off_bwd_esg_ = 0, off_bwd_eb_ = 0, off_bwd_table_ = 0, off_bwd_gtable_ = 0,
-           off_bwd_partial_ = 0;
+           off_bwd_partial_ = 0, off_bwd_bias_ = 0;
     int activation_ = 0;
     int* nan_flag_ = nullptr;  // device int, owned
     int crop_ = 0;             // (kernel_size-1)/2 - pad

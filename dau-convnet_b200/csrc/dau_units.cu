@@ -97,10 +97,13 @@ __global__ void grad_finalize_kernel(GradFinalizeArgs a) {
 }
 
 // dbias[f] += sum_{n,hw} err[n,f,hw]   (reference: cublasSgemv with a ones vector,
-// base_dau_conv_layer.cpp:1116-1126).  grid = (F, image slices); with `act` the error counts only
-// where the activation output was positive (ReLU backward fused into the load).
+// base_dau_conv_layer.cpp:1116-1126).  Two stages, no atomics: grid = (F, image slices) writes one
+// partial per (slice, f) into the workspace, bias_finalize_kernel adds them in slice order -- the
+// same bits on every run.  With `act` the error counts only where the activation output was positive
+// (ReLU backward fused into the load).
+constexpr int kBiasSlices = 16;
 __global__ void __launch_bounds__(256) bias_grad_kernel(const float* __restrict__ err, const float* __restrict__ act,
-                                                       float* dbias, int N, int F, int HW) {
+                                                       float* __restrict__ partial, int N, int F, int HW) {
     const int f = blockIdx.x;
     float acc = 0.f;
     for (int n = blockIdx.y; n < N; n += gridDim.y) {
@@ -118,8 +121,15 @@ __global__ void __launch_bounds__(256) bias_grad_kernel(const float* __restrict_
     if (threadIdx.x == 0) {
         float t = 0.f;
         for (int i = 0; i < 8; ++i) t += red[i];
-        atomicAdd(dbias + f, t);
+        partial[(size_t)blockIdx.y * F + f] = t;
     }
+}
+__global__ void bias_finalize_kernel(const float* __restrict__ partial, float* dbias, int F, int slices) {
+    const int f = blockIdx.x * blockDim.x + threadIdx.x;
+    if (f >= F) return;
+    float t = 0.f;
+    for (int s = 0; s < slices; ++s) t += partial[(size_t)s * F + f];
+    dbias[f] += t;
 }
 
 // 8 independent FFMA chains per thread, register resident: measures the FP32 FMA pipe.
@@ -162,9 +172,13 @@ void launch_grad_finalize(const GradFinalizeArgs& a, cudaStream_t stream) {
     DAU_CUDA_CHECK(cudaGetLastError());
 }
 
-void launch_bias_grad(const float* err, const float* act, float* dbias, int N, int F, int HW, cudaStream_t stream) {
-    const int slices = N < 16 ? N : 16;
-    bias_grad_kernel<<<dim3(F, slices), 256, 0, stream>>>(err, act, dbias, N, F, HW);
+size_t bias_grad_partial_floats(int F) { return (size_t)kBiasSlices * F; }
+
+void launch_bias_grad(const float* err, const float* act, float* dbias, float* partial, int N, int F, int HW,
+                      cudaStream_t stream) {
+    const int slices = N < kBiasSlices ? N : kBiasSlices;
+    bias_grad_kernel<<<dim3(F, slices), 256, 0, stream>>>(err, act, partial, N, F, HW);
+    bias_finalize_kernel<<<(F + 127) / 128, 128, 0, stream>>>(partial, dbias, F, slices);
     DAU_CUDA_CHECK(cudaGetLastError());
 }
 

@@ -228,6 +228,15 @@ def _check_inputs(x, w, mu1, mu2, sigma, attrs):
             raise RuntimeError("DAUConv: %s has shape %s, expected %s" % (name, tuple(t.shape), want))
 
 
+def _param_flags(attrs):
+    """params_propagate_down of the reference's grad op: with single_dim_kernel it passes false for mu2
+    and returns zeros for it (dau_conv_grad_op.cpp:291-292)."""
+    f = _lib.GRAD_W | _lib.GRAD_MU1 | _lib.GRAD_SIGMA
+    if not attrs.get("single_dim_kernel", False):
+        f |= _lib.GRAD_MU2
+    return f
+
+
 def _sigma_of(sigma, sigma_value):
     # the TF op builds its layer from the live sigma (one number per layer); a caller that knows
     # the value passes it and spares the blocking device read
@@ -255,7 +264,7 @@ def dau_conv_grad_op(grad, input, weights, mu1, mu2, sigma, sigma_value=None, ma
     h.set_sigma_hint(_sigma_of(sigma, sigma_value))
     h.set_offset_hint(max_offset)
     return h.backward(input.contiguous(), grad.contiguous(), weights.contiguous(), mu1.contiguous(),
-                      mu2.contiguous(), sigma.contiguous())
+                      mu2.contiguous(), sigma.contiguous(), flags=_lib.GRAD_INPUT | _param_flags(attrs))
 
 
 class _DAUConvFunction(torch.autograd.Function):
@@ -277,7 +286,7 @@ class _DAUConvFunction(torch.autograd.Function):
         if need[0]:
             flags |= _lib.GRAD_INPUT
         if any(need[1:5]):
-            flags |= _lib.GRAD_W | _lib.GRAD_MU1 | _lib.GRAD_MU2 | _lib.GRAD_SIGMA
+            flags |= _param_flags(ctx.attrs)
         _check_inputs(input, weights, mu1, mu2, sigma, ctx.attrs)
         h = get_handle(input.device, **ctx.attrs)
         h.set_sigma_hint(ctx.sigma_value)
@@ -321,7 +330,7 @@ class _DAUConvFusedFunction(torch.autograd.Function):
         if need[0]:
             flags |= _lib.GRAD_INPUT
         if any(need[1:5]):
-            flags |= _lib.GRAD_W | _lib.GRAD_MU1 | _lib.GRAD_MU2 | _lib.GRAD_SIGMA
+            flags |= _param_flags(ctx.attrs)
         dbias = None
         if need[5]:
             flags |= _lib.GRAD_BIAS

@@ -114,6 +114,7 @@ class DAUConv2d(nn.Module):
         self.mean_max_allowed_offset = math.floor(self.max_kernel_size / 2.0) - self.dau_unit_border_bound
         self.weights = self.mu1 = self.mu2 = self.sigma = self.bias = None
         self._sigma_value = None             # host copy of sigma: spares the op a device read per call
+        self._sigma_key = None               # (id, version) of the sigma parameter the copy was read from
         if in_channels is not None:
             self.build(in_channels)
 
@@ -175,8 +176,12 @@ class DAUConv2d(nn.Module):
         mu1 = self.mu1.clamp(-lim, lim)                       # :185-186 (clipping is part of the graph)
         mu2 = self.mu2.clamp(-lim, lim)
         sigma = self.sigma.reshape(1, 1, 1, 1).expand(self.weights.shape)      # tiled view (:418-430)
-        if self.dau_sigma_trainable or self._sigma_value is None:
-            self._sigma_value = float(self.sigma.detach().reshape(-1)[0])      # one blocking read
+        # host copy of sigma, refreshed whenever the parameter object or its version counter changed
+        # (optimizer step, load_state_dict, in-place edit): one blocking read per change, none otherwise
+        key = (id(self.sigma), self.sigma._version)
+        if self._sigma_value is None or self._sigma_key != key:
+            self._sigma_value = float(self.sigma.detach().reshape(-1)[0])
+            self._sigma_key = key
         # bias add and ReLU (:500-526) are element-wise, so they commute with the stride slicing and
         # run inside the operator's own kernels; any other activation is applied afterwards
         relu = self.activation in (torch.relu, nn.functional.relu) or isinstance(self.activation, nn.ReLU)

@@ -5,8 +5,13 @@
  * BaseDAUConvLayer<float>::Forward_gpu / Backward_gpu and the TensorFlow ops
  * DAUConv / DAUConvGrad built on top of them.  Plain pointers and sizes only; every
  * pointer named *_dev is DEVICE memory owned by the caller, every call is ordered on
- * the caller's CUDA stream (passed as void*; NULL = legacy default stream), nothing is
- * allocated behind the caller's back except a few KB of per-handle constant tables.
+ * the caller's CUDA stream (passed as void*; NULL = legacy default stream).  dau_forward /
+ * dau_backward allocate nothing behind the caller's back except 4 bytes per handle (the NaN flag);
+ * the *_host conveniences are the exception and say so: dau_forward_host / dau_backward_host
+ * cudaMalloc and free their device copies inside the call, and dau_train_step_host keeps a device
+ * pool per handle (two staging buffers per tensor plus the workspace of the largest chunk, sized on
+ * first use; growing it synchronises the device once) until dau_destroy.  Every entry point leaves
+ * the calling thread's current CUDA device as it found it.
  *
  * Reference interfaces replaced (paths relative to the reference checkout):
  *   dau_settings_t      <- DAUConvSettings                   include/dau_conv/base_dau_conv_layer.hpp:109-130
@@ -189,6 +194,22 @@ dau_status_t dau_train_step_host(dau_handle_t* h, int N, int S, int H, int W, in
  * image pixels, 0 for gap pixels and for cells beyond the batch. */
 dau_status_t dau_plan_mosaic(int N, int H, int W, int gap, int* out10);
 int dau_mosaic_to_real(const int* mosaic10, int N, int nv, int vy, int vx, int* n, int* y, int* x);
+
+/* ignore_edge_gradients rule for one output extent: 1 if the last row / column of the top error is
+ * zeroed (extent a multiple of the reference's patch size 64 / 32 / 16 / 8, the largest that is
+ * <= extent; plugins/tensorflow/tests/dau_conv_test.py:110-136, base_dau_conv_layer.cpp:763-771). */
+int dau_edge_mask_rule(int extent);
+
+/* Test hook (integer-only model of the index math, SURVEY section 8(d) parity gate): the unit tables
+ * the kernels read for these DEVICE parameters [1,S,G,F], written into caller-provided DEVICE buffers
+ * of S*G*F 32-byte records {float w00, w01, w10, w11; int32 offx + halo_x, offy + halo_y, 0, 0} (any of
+ * the three may be NULL).  Orders: forward [s][f][g] (offset floor(mu), dau_conv_forward_core.hpp:2025-2028,
+ * weights w * bilinear(frac), :2155-2213), back-propagation [f][s][g] (offset floor(-mu)), gradient
+ * [s][f][g] (offset -floor(mu)-1, bilinear weights flipped, no w).  halos4_host = {halo_x, halo_y of the
+ * first two tables, halo_x, halo_y of the gradient table}.  After dau_reshape. */
+dau_status_t dau_debug_unit_tables(dau_handle_t* h, const float* w_dev, const float* mu1_dev,
+                                   const float* mu2_dev, void* fwd_out_dev, void* bwd_out_dev,
+                                   void* grad_out_dev, int* halos4_host, void* stream);
 
 /* Measurement helpers used by bench.py (not part of the reference contract). */
 dau_status_t dau_measure_fma_peak(int device, int iters, double* tflops_out, double* ms_out);

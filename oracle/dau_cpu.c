@@ -40,6 +40,15 @@ int dau_cpu_num_threads(void) {
 #endif
 }
 
+/* bench.py's reference arm: torch.distributed.run exports OMP_NUM_THREADS=1 to its workers */
+void dau_cpu_set_num_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 int dau_cpu_kernel_size(float sigma) { return 2 * (int)ceilf(5.0f * sigma) + 1; }
 
 /* six Kb x Kb double filters: blur, d_w, d_mu1, d_mu2, d_sigma, d_error (axis 0 = y) */

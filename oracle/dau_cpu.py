@@ -15,6 +15,8 @@ def load():
         subprocess.check_call(["make", "-C", _HERE])
     lib = C.CDLL(_SO)
     lib.dau_cpu_num_threads.restype = C.c_int
+    lib.dau_cpu_set_num_threads.argtypes = [C.c_int]
+    lib.dau_cpu_set_num_threads.restype = None
     lib.dau_cpu_filters.argtypes = [C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int),
                                     np.ctypeslib.ndpointer(np.float64, flags="C_CONTIGUOUS")]
     lib.dau_cpu_forward.argtypes = [_fp, _fp, _fp, _fp, C.c_float] + [C.c_int] * 12 + [_fp]

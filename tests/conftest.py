@@ -9,7 +9,7 @@ import sys
 import pytest
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-for p in (ROOT, os.path.join(ROOT, "dau-convnet_b200")):
+for p in (ROOT, os.path.join(ROOT, "dau-convnet_b200"), os.path.join(ROOT, "tests")):
     if p not in sys.path:
         sys.path.insert(0, p)
 
@@ -35,3 +35,26 @@ def pytest_collection_modifyitems(config, items):
 @pytest.fixture(scope="session")
 def golden_dir():
     return os.path.join(ROOT, "tests", "golden")
+
+
+def pytest_terminal_summary(terminalreporter):
+    """How large the parameter-gradient tolerance concession actually is (tests/_tolerance.py)."""
+    try:
+        import json
+        import _tolerance
+    except Exception:  # pragma: no cover
+        return
+    lines = _tolerance.summary_lines()
+    if not lines:
+        return
+    terminalreporter.section("parity tolerance bookkeeping")
+    for ln in lines:
+        terminalreporter.write_line(ln)
+    try:
+        out = os.path.join(ROOT, "gpurun_out")
+        os.makedirs(out, exist_ok=True)
+        with open(os.path.join(out, "strict_tolerance.json"), "w") as f:
+            json.dump({k: dict(calls=v[0], elements=v[1], outside_unscaled_rule=v[2], worst_ratio=v[3],
+                               max_abs_ref=v[4]) for k, v in _tolerance.REPORT.items()}, f, indent=1, sort_keys=True)
+    except OSError:
+        pass

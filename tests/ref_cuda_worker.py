@@ -3,7 +3,8 @@ The reference build aborts the process on shapes outside what its authors tested
 destructor after a faulting kernel), so tests never load it in-process: tests/ref_cuda.py run_isolated()
 spawns this file.  No torch here: device memory through libcudart via ctypes.
 usage: python tests/ref_cuda_worker.py <dir>   (reads <dir>/in.npz, writes <dir>/out.npz)
-       python tests/ref_cuda_worker.py --kernels <sigma> <flags> <out.npy>"""
+       python tests/ref_cuda_worker.py --kernels <sigma> <flags> <out.npy>
+       python tests/ref_cuda_worker.py --bench <bench.py config> <images> <iters> <out.json>   (timing only)"""
 import ctypes
 import os
 import sys
@@ -30,11 +31,28 @@ def kernels_main(sigma, flags, out_path):
     np.save(out_path, buf[:6 * k * k].reshape(6, k, k))
 
 
+def bench_inputs(cfg, n_images):
+    """bench.py's synthetic tensors for one of its configurations (no file round trip)."""
+    sys.path.insert(0, os.path.dirname(HERE))
+    import bench
+    N, S, F, units, H, W, ks, m = bench.CONFIGS[cfg]
+    x, e, w, mu1, mu2 = bench.make_inputs_numpy(cfg, n_images, 1234)
+    return dict(x=x, err=e, w=w, mu1=mu1, mu2=mu2, sigma=np.full(w.shape, 0.5, np.float32),
+                meta=np.array([units[0], units[1], ks, 1, 0, 1, 0]), mu_lr=np.float32(1.0))
+
+
 def main():
     if sys.argv[1] == "--kernels":
         return kernels_main(float(sys.argv[2]), int(sys.argv[3]), sys.argv[4])
-    d = sys.argv[1]
-    z = np.load(os.path.join(d, "in.npz"))
+    bench_out = None
+    if sys.argv[1] == "--bench":
+        z = bench_inputs(sys.argv[2], int(sys.argv[3]))
+        z["meta"][5] = int(sys.argv[4])
+        bench_out = sys.argv[5]
+        d = None
+    else:
+        d = sys.argv[1]
+        z = np.load(os.path.join(d, "in.npz"))
     rt = ctypes.CDLL("libcudart.so.12")
     rt.cudaMalloc.argtypes = [ctypes.POINTER(ctypes.c_void_p), ctypes.c_size_t]
     rt.cudaMemcpy.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int]
@@ -81,6 +99,11 @@ def main():
     if rc != 0:
         sys.stderr.write("reference CUDA path refused: " + msg.value.decode(errors="replace") + "\n")
         sys.exit(3)
+    if bench_out is not None:
+        import json
+        with open(bench_out, "w") as f:
+            json.dump({"fwd_ms": fwd.value, "bwd_ms": bwd.value, "workspace_bytes": int(ws.value), "iters": iters}, f)
+        return
     np.savez(os.path.join(d, "out.npz"), y=down(py, (N, F, H, W)), dx=down(pdx, x.shape),
              dw=down(pg[0], w.shape), dmu1=down(pg[1], w.shape), dmu2=down(pg[2], w.shape),
              dsigma=down(pg[3], w.shape), info=np.array([fwd.value, bwd.value, float(ws.value)]))

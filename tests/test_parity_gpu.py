@@ -18,18 +18,7 @@ pytestmark = pytest.mark.gpu
 HERE = os.path.dirname(os.path.abspath(__file__))
 GOLDEN = sorted(p for p in glob.glob(os.path.join(HERE, "golden", "*.npz"))
                 if not os.path.basename(p).startswith("filters_"))
-RTOL, ATOL = 1e-4, 1e-5
-
-
-def close(got, ref, name, scale_atol=False):
-    got = np.asarray(got, np.float64)
-    ref = np.asarray(ref, np.float64)
-    assert got.shape == ref.shape, name
-    atol = ATOL * (max(1.0, float(np.abs(ref).max())) if scale_atol else 1.0)
-    err = np.abs(got - ref)
-    bad = err > atol + RTOL * np.abs(ref)
-    assert not bad.any(), "%s: %d/%d outside tolerance, max abs err %.3e (max|ref| %.3e)" % (
-        name, int(bad.sum()), bad.size, float(err.max()), float(np.abs(ref).max()))
+from _tolerance import ATOL, RTOL, close  # noqa: E402,F401  (the rule and its bookkeeping)
 
 
 def run_layer(x, err, w, mu1, mu2, sigma, ks, **attrs):

@@ -1,8 +1,12 @@
 """Parity of this repo's CUDA path against the REFERENCE'S OWN CUDA kernels, both run on the same GPU
 on the same inputs.  oracle/_ref/libdau_ref_cuda.so is the reference's BaseDAUConvLayer<float> built
-for sm_100a from the sources under /root/reference (oracle/Makefile.refcuda; only the kernel-template
-7 of the 11 forward and 8 of the 17 gradient kernel-template shards are
-compiled, so the shapes below stay inside them).
+for sm_100a from the sources under /root/reference (oracle/Makefile.refcuda).  Round 2 compiles all 11
+forward and 17 gradient kernel-template shards (oracle/_ref/shards.txt lists what a given build holds):
+CASES stay inside the 15 shards round 1 had, EXTRA_CASES dispatch to the other 13 (F not a multiple of
+16 / odd S at offsets above 4 px, 1x1 and 8xN / Nx8 patches).  A reference call that ends with "shard
+not built" FAILS the test when shards.txt says the build is complete; a reference process that dies
+inside its own kernels is recorded as a reference fault (xfail) -- this repo is held to the oracle on
+every shape before the reference is asked.
 
 Two bars, both written here:
  * the reference's own acceptance rule for its CUDA op against its NumPy model
@@ -17,6 +21,7 @@ is from it.
 import numpy as np
 import pytest
 
+import _tolerance
 import ref_cuda
 from oracle import dau_oracle as O
 
@@ -35,11 +40,7 @@ def reference_assert_matrix(mat, gt, name, rel_tolerance=0.01):
 
 
 def strict(got, ref, name, scale_atol=False):
-    atol = 1e-5 * (max(1.0, float(np.abs(ref).max())) if scale_atol else 1.0)
-    err = np.abs(got.astype(np.float64) - ref.astype(np.float64))
-    bad = err > atol + 1e-4 * np.abs(ref)
-    assert not bad.any(), "%s: %d/%d outside 1e-4 rel / %.1e abs, max abs err %.3e (max|ref| %.3e)" % (
-        name, int(bad.sum()), bad.size, atol, float(err.max()), float(np.abs(ref).max()))
+    return _tolerance.close(got, ref, "refcuda:" + name, scale_atol=scale_atol)
 
 
 # shapes on which the reference build (as compiled here for sm_100a) itself faults: illegal memory access inside its
@@ -49,6 +50,29 @@ REFERENCE_FAULTS = {
     (2, 15, 32, (1, 2), 32, 32, 9),        # odd S
     (2, 16, 32, (1, 2), 64, 64, 33),       # the 16-px offset bucket (8 px and 32 px run)
 }
+
+
+def _all_shards_built():
+    import os
+    p = os.path.join(os.path.dirname(ref_cuda.SO), "shards.txt")
+    return os.path.exists(p) and len(open(p).read().split()) >= 28
+
+
+# shapes that dispatch to the 13 shards round 1 had not compiled (src/dau_conv/dau_conv_impl/dau_conv_forward.cpp:
+# single_feature = F % 16 != 0, single_subfeature = S odd; dau_conv_backward.cpp:15-36: patch 8 / 16 / 32 / 64 per
+# axis from the map extent, 1x1 for 1x1 maps).  The reference's authors never ran most of them: a reference
+# process that dies is an expected outcome here, a "shard not built" answer is not.
+EXTRA_CASES = [
+    (2, 15, 32, (1, 2), 32, 32, 17),       # forward off8 s0_f1 ; dL/dx off8 s1_f0
+    (2, 16, 40, (1, 2), 32, 32, 17),       # forward off8 s1_f0
+    (2, 15, 40, (1, 2), 32, 32, 17),       # forward off8 s1_f1
+    (2, 15, 40, (1, 2), 64, 64, 33),       # forward off16 s1_f1
+    (4, 16, 32, (1, 2), 8, 16, 9), (4, 16, 32, (1, 2), 16, 8, 9),          # 8x16 / 16x8 patches
+    (4, 16, 32, (1, 2), 8, 32, 9), (4, 16, 32, (1, 2), 32, 8, 9),          # 8x32 / 32x8
+    (2, 16, 32, (1, 2), 8, 64, 9), (2, 16, 32, (1, 2), 64, 8, 9),          # 8x64 / 64x8
+    (2, 16, 32, (1, 2), 16, 64, 9), (2, 16, 32, (1, 2), 64, 16, 9),        # 16x64 / 64x16
+    (8, 16, 32, (1, 2), 1, 1, 9),                                          # 1x1 maps
+]
 
 CASES = [
     # N, S, F, (Gx, Gy), H, W, kernel_size   (the reference's gradient kernel needs F >= 32)
@@ -70,7 +94,8 @@ CASES = [
 ]
 
 
-@pytest.mark.parametrize("case", CASES, ids=lambda c: "N%dS%dF%dG%dx%d_%dx%d_k%d" % (c[0], c[1], c[2], c[3][0], c[3][1], c[4], c[5], c[6]))
+@pytest.mark.parametrize("case", CASES + EXTRA_CASES,
+                         ids=lambda c: "N%dS%dF%dG%dx%d_%dx%d_k%d" % (c[0], c[1], c[2], c[3][0], c[3][1], c[4], c[5], c[6]))
 def test_matches_reference_cuda(case, tmp_path):
     import torch
     import dau_conv
@@ -98,13 +123,19 @@ def test_matches_reference_cuda(case, tmp_path):
     g_o = O.backward(x, err, w, mu1, mu2, [0.5], ignore_edge_gradients=True)
     strict(ours[0], y_o, "top vs oracle")
     strict(ours[1], g_o[0], "bottom_error vs oracle", scale_atol=True)
+    for k, name in enumerate(["dw", "dmu1", "dmu2", "dsigma"]):
+        strict(ours[2 + k], g_o[1 + k], name + " vs oracle", scale_atol=True)
 
     try:
         r = ref_cuda.run_isolated(x, err, w, mu1, mu2, sigma, units, tmp_path, kernel_size=ks,
                                   ignore_edge_gradients=True)
     except ref_cuda.ReferenceFault as ex:
-        if case in REFERENCE_FAULTS:
-            pytest.xfail("the reference's own CUDA build dies on this shape (%s); this repo matches the oracle" % ex)
+        if "not built" in str(ex):
+            assert not _all_shards_built(), "complete reference build still answers 'shard not built': %s" % ex
+            pytest.skip("this oracle/_ref build lacks the shard this shape dispatches to (%s)" % ex)
+        if case in REFERENCE_FAULTS or case in EXTRA_CASES:
+            pytest.xfail("reference fault: the reference's own CUDA build dies on this shape (%s); this repo "
+                         "matches the oracle" % ex)
         raise
     if case in REFERENCE_FAULTS:
         # an out-of-bounds access does not fault on every box: when the reference survives, its numbers on such a

@@ -9,9 +9,21 @@ in the tree, so the layer shapes are the derivation of SURVEY.md section 8(d), a
 conv1 11x11/4 (torch/cuDNN) -> ReLU -> LRN -> pool -> DAU L2 (96->256 @27x27) -> ReLU -> LRN ->
 pool -> DAU L3 (256->384 @13x13) -> DAU L4 (384->384) -> DAU L5 (384->256) -> pool -> FC x3.
 `default` has 2 units per (s,f) pair (0.74 M units), `large` 4 (1.47 M).  The four DAU layers run
-on libdau_conv_b200.so through dau_conv.DAUConv2d; everything else is stock torch.  One step =
-forward, loss, backward, ONE bucketed NCCL all-reduce of all gradients, SGD update, on synthetic
-data.  Prints one JSON line (whole-job images/s, max over ranks, CUDA events).
+on libdau_conv_b200.so through dau_conv.DAUConv2d; everything else is stock torch.
+
+One step = forward, loss, backward, all-reduce of ALL gradients, SGD(momentum) update, on synthetic
+data.  How the step is laid out (`Trainer`):
+  * parameters, gradients and momentum live in two flat buffers each -- "head" (the three FC layers,
+    235 MB, 95 % of the bytes) and "body" (conv1 + the DAU layers) -- so a bucket is ONE all-reduce and
+    the optimizer is two element-wise kernels per bucket instead of three per parameter;
+  * the loss is sum_i CE_i / global_batch, so per-rank gradients ADD to the single-GPU gradient: the
+    all-reduce is a plain SUM, uneven shards are exact, nothing is divided afterwards;
+  * backward runs in two pieces: through the FC head first, whose bucket is all-reduced (NCCL, async,
+    its own stream) WHILE the backward pass of the convolutional body runs; the small body bucket
+    follows.  The DAU layers' [4,S,G,F] gradients are all that leaves a GPU for the path itself;
+  * with graph=True the whole step (both collectives included) is captured once in a CUDA graph and
+    replayed: at 32 images per GPU the step is ~150 launches of a few tens of microseconds each.
+Prints one JSON line (whole-job images/s, max over ranks, CUDA events).
 """
 import argparse
 import json
@@ -19,13 +31,17 @@ import os
 import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-sys.path.insert(0, os.path.join(ROOT, "dau-convnet_b200"))
+for _p in (os.path.join(ROOT, "dau-convnet_b200"),):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
 
 import torch
 import torch.distributed as dist
 from torch import nn
 
 import dau_conv
+
+VARIANTS = {"default": (1, 2), "large": (2, 2)}
 
 
 class AlexNetDAU(nn.Module):
@@ -45,21 +61,175 @@ class AlexNetDAU(nn.Module):
         return self.classifier(self.features(x))
 
 
+class _Bucket(object):
+    """Parameters, gradients and momentum of a group of parameters as three flat fp32 buffers; the
+    parameters' .data and .grad are views into them."""
+
+    def __init__(self, params, device):
+        self.params = [p for p in params if p.requires_grad]
+        n = sum(p.numel() for p in self.params)
+        self.p = torch.empty(n, device=device); self.g = torch.zeros(n, device=device)
+        self.m = torch.zeros(n, device=device)
+        o = 0
+        for p in self.params:
+            k = p.numel()
+            self.p[o:o + k].copy_(p.data.reshape(-1))
+            p.data = self.p[o:o + k].view_as(p)
+            p.grad = self.g[o:o + k].view_as(p)
+            o += k
+
+    def sgd(self, lr, momentum):
+        self.m.mul_(momentum).add_(self.g)
+        self.p.add_(self.m, alpha=-lr)
+
+
+class Trainer(object):
+    def __init__(self, variant="default", global_batch=256, device=None, rank=0, world=1, lr=1e-3, momentum=0.9,
+                 overlap=True, graph=False, seed=1234, num_classes=1000, data_seed=99):
+        self.rank, self.world, self.global_batch = rank, world, int(global_batch)
+        self.dev = torch.device(device if device is not None else "cuda")
+        self.lr, self.momentum, self.overlap = lr, momentum, bool(overlap)
+        torch.manual_seed(seed)                                   # identical parameters on every rank
+        self.model = AlexNetDAU(VARIANTS[variant], num_classes).to(self.dev)
+        self.head = _Bucket(self.model.classifier.parameters(), self.dev)
+        self.body = _Bucket(self.model.features.parameters(), self.dev)
+        # images [lo, hi) of the global batch (dau_conv.distributed.shard_range: uneven shards allowed)
+        from dau_conv.distributed import shard_range
+        self.lo, self.hi = shard_range(self.global_batch, rank, world)
+        gen = torch.Generator(device="cpu"); gen.manual_seed(data_seed)
+        # synthetic data: the SAME global batch whatever the rank count (strong scaling, comparable runs)
+        self.x = None; self.target = None
+        self._gen = gen
+        self.n_dau_units = sum(m.weights.numel() for m in self.model.modules() if isinstance(m, dau_conv.DAUConv2d))
+        self.num_classes = num_classes
+        self._graph = None
+        self._want_graph = bool(graph)
+        self.graph_error = None
+        self._loss = None
+
+    # -- data -------------------------------------------------------------------------------------------
+    def set_batch(self, x_global=None, target_global=None):
+        """This rank's shard of a global batch (synthetic uniform images / random labels by default)."""
+        if x_global is None:
+            x_global = torch.rand((self.global_batch, 3, 227, 227), generator=self._gen)
+            target_global = torch.randint(0, self.num_classes, (self.global_batch,), generator=self._gen)
+        x = x_global[self.lo:self.hi].to(self.dev); t = target_global[self.lo:self.hi].to(self.dev)
+        if self.x is None or self.x.shape != x.shape:
+            self.x, self.target = x.contiguous(), t.contiguous()
+            self._graph = None
+        else:                                                     # keep the addresses a captured graph reads
+            self.x.copy_(x); self.target.copy_(t)
+
+    # -- one step -----------------------------------------------------------------------------------------
+    def _reduce(self, bucket):
+        if self.world > 1 and dist.is_available() and dist.is_initialized():
+            return dist.all_reduce(bucket.g, op=dist.ReduceOp.SUM, async_op=True)
+        return None                                               # one rank (or shards simulated on one GPU by a test)
+
+    def compute_gradients(self):
+        """Forward + backward of this rank's shard; leaves the SUMMED (all-reduced) gradients of the global
+        batch in the flat buffers and returns the shard's part of the loss."""
+        m = self.model
+        self.head.g.zero_(); self.body.g.zero_()
+        f = m.features(self.x)
+        fd = f.detach().requires_grad_(True)
+        loss = nn.functional.cross_entropy(m.classifier(fd), self.target, reduction="sum") / self.global_batch
+        loss.backward()                                           # FC head: its bucket is complete now
+        w_head = self._reduce(self.head) if self.overlap else None
+        f.backward(fd.grad)                                       # convolutional body, under the head's all-reduce
+        if not self.overlap:
+            w_head = self._reduce(self.head)
+        w_body = self._reduce(self.body)
+        for w in (w_head, w_body):
+            if w is not None:
+                w.wait()                                          # stream-ordered: the compute stream waits, not the host
+        return loss.detach()
+
+    def _eager_step(self):
+        loss = self.compute_gradients()
+        self.head.sgd(self.lr, self.momentum); self.body.sgd(self.lr, self.momentum)
+        return loss
+
+    def capture(self, warmup=3):
+        """Captures the step in a CUDA graph (collectives included); falls back to eager on failure."""
+        side = torch.cuda.Stream(self.dev)
+        side.wait_stream(torch.cuda.current_stream(self.dev))
+        with torch.cuda.stream(side):
+            for _ in range(warmup):
+                self._eager_step()
+        torch.cuda.current_stream(self.dev).wait_stream(side)
+        torch.cuda.synchronize(self.dev)
+        if self.world > 1 and dist.is_initialized():
+            dist.barrier()
+        try:
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._loss = self._eager_step()
+            self._graph = g
+        except Exception as ex:                                   # pragma: no cover  (reported by the caller)
+            self._graph = None
+            self.graph_error = "%s: %s" % (type(ex).__name__, str(ex)[:300])
+            torch.cuda.synchronize(self.dev)
+
+    def step(self):
+        if self.x is None:
+            self.set_batch()
+        if self._want_graph and self._graph is None and self.graph_error is None:
+            self.capture()
+        if self._graph is not None:
+            self._graph.replay()
+            return self._loss
+        return self._eager_step()
+
+    def global_loss(self, loss):
+        """Sum of the ranks' loss parts = the mean loss of the global batch."""
+        t = loss.detach().clone().reshape(1)
+        if self.world > 1 and dist.is_initialized():
+            dist.all_reduce(t)
+        return float(t.item())
+
+    # -- timing ---------------------------------------------------------------------------------------------
+    def sync(self):
+        torch.cuda.synchronize(self.dev)
+        if self.world > 1 and dist.is_initialized():
+            dist.barrier()
+        torch.cuda.synchronize(self.dev)
+
+    def timed(self, steps, warmup):
+        """(ms per step as the max over ranks, last global loss): CUDA events around `steps` steps."""
+        loss = None
+        for _ in range(max(warmup, 1)):
+            loss = self.step()
+        self.sync()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            loss = self.step()
+        e1.record()
+        self.sync()
+        t = torch.tensor([e0.elapsed_time(e1)], device=self.dev)
+        if self.world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item()) / steps, self.global_loss(loss)
+
+    def describe(self, variant):
+        return ("AlexNet-DAU-%s, %d DAU units, global batch %d at 227x227, batch-sharded dp%d (%d images on rank 0), "
+                "SUM all-reduce of two flat gradient buckets (FC head %s the backward pass of the body) + SGD momentum, %s"
+                % (variant, self.n_dau_units, self.global_batch, self.world, self.hi - self.lo,
+                   "overlapped with" if self.overlap else "after",
+                   "one CUDA graph per rank" if self._graph is not None else "eager launches"))
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--variant", default="default", choices=["default", "large"])
+    ap.add_argument("--variant", default="default", choices=sorted(VARIANTS))
     ap.add_argument("--global-batch", type=int, default=256)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--overlap", type=int, default=1,
-                    help="1: gradient buckets are all-reduced while backward still runs (torch DDP); "
-                         "0: one all-reduce of all gradients after backward")
-    ap.add_argument("--graph", type=int, default=0,
-                    help="1: capture forward + backward + SGD of one rank in a CUDA graph (single GPU only)")
-    ap.add_argument("--lean", type=int, default=1,
-                    help="1: gradients are dropped, not zero-filled, between steps (autograd then assigns instead of "
-                         "accumulating: no fill and no add per parameter) and SGD runs as one fused kernel per "
-                         "parameter group; 0: zero-filled gradients and the foreach SGD")
+                    help="1: the FC head's gradient bucket is all-reduced while the body's backward pass runs; "
+                         "0: both buckets after backward")
+    ap.add_argument("--graph", type=int, default=1, help="1: replay the step as one CUDA graph per rank; 0: eager")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -68,77 +238,15 @@ def main():
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
-    torch.manual_seed(1234)                                    # identical parameters on every rank
-    units = (1, 2) if args.variant == "default" else (2, 2)
-    model = AlexNetDAU(units).to(dev)
-    net = model
-    if world > 1 and args.overlap:
-        net = nn.parallel.DistributedDataParallel(model, device_ids=[local], bucket_cap_mb=32,
-                                                  gradient_as_bucket_view=True)
-    n_local = args.global_batch // world
-    gen = torch.Generator(device=dev); gen.manual_seed(99 + rank)
-    x = torch.rand((n_local, 3, 227, 227), device=dev, generator=gen)
-    target = torch.randint(0, 1000, (n_local,), device=dev, generator=gen)
-    params = [p for p in model.parameters() if p.requires_grad]
-    opt = torch.optim.SGD(params, lr=1e-3, momentum=0.9, fused=bool(args.lean))
-    n_dau_units = sum(m.weights.numel() for m in model.modules() if isinstance(m, dau_conv.DAUConv2d))
-
-    def step():
-        opt.zero_grad(set_to_none=bool(args.lean))
-        loss = nn.functional.cross_entropy(net(x), target)
-        loss.backward()
-        if world > 1 and not args.overlap:                     # one bucket: all gradients, summed, / world
-            flat = torch.cat([p.grad.reshape(-1) for p in params])
-            dist.all_reduce(flat)
-            flat /= world
-            o = 0
-            for p in params:
-                p.grad.copy_(flat[o:o + p.numel()].view_as(p)); o += p.numel()
-        opt.step()
-        return loss
-
-    def sync():
-        torch.cuda.synchronize(dev)
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize(dev)
-
-    for _ in range(args.warmup):
-        step()
-    sync()
-    if args.graph and world == 1:
-        # everything in the step is stream-ordered and allocation-free after warm-up (the DAU op reads
-        # no device value on the host once sigma is known), so the whole step replays as one graph
-        graph = torch.cuda.CUDAGraph()
-        eager_step = step
-        with torch.cuda.graph(graph):
-            static_loss = eager_step()
-
-        def step():
-            graph.replay()
-            return static_loss
-        step()
-        sync()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(args.steps):
-        loss = step()
-    e1.record()
-    sync()
-    t = torch.tensor([e0.elapsed_time(e1)], device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t.item()) / args.steps
+    tr = Trainer(args.variant, args.global_batch, dev, rank, world, overlap=bool(args.overlap), graph=bool(args.graph))
+    ms, loss = tr.timed(args.steps, args.warmup)
     if rank == 0:
         print(json.dumps({
             "metric": "alexnet_dau_train_step_images_per_sec", "value": args.global_batch / (ms * 1e-3),
             "unit": "images/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
-            "scaling": "strong", "dtype": "f32", "data": "synthetic", "loss": float(loss),
-            "config": {"workload": "AlexNet-DAU-%s, %d DAU units, global batch %d at 227x227, batch-sharded dp%d, "
-                                   "%s + SGD" % (
-                                       args.variant, n_dau_units, args.global_batch, world,
-                                       "bucketed NCCL all-reduce overlapped with backward" if args.overlap
-                                       else "one NCCL all-reduce of all gradients")}}))
+            "scaling": "strong", "dtype": "f32", "data": "synthetic", "loss": loss,
+            "graph": tr._graph is not None, "graph_error": tr.graph_error,
+            "config": {"workload": tr.describe(args.variant)}}))
     if world > 1:
         dist.destroy_process_group()
 
