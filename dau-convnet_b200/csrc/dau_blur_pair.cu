@@ -55,7 +55,9 @@ struct PairBlurArgs {
     float2 fy[3][PT_MAXTAPS];    // column filters as (f, f): tap v applies to row y + v - c
     int H, W, N, Cn, z0;         // H, W, N: mosaic extents
     Mosaic m;                    // mosaic <-> real image mapping (identity for wide images)
-    int tiles_x, tiles_y;        // XS: 64-column / 4-row item grid
+    int tiles_x;                 // XS: 64-column tiles
+    int sq, stail;               // XS: full 4-row strips per cell row, rows of the tail strip (StripGeom)
+    long long tail_base;         // XS: float offset of the tail blocks
     int qp, qv;                  // PG: padded / valid float2-columns per plane
     // MODE 2 extras (the top error on its way into the backward pass):
     const float* mask;           // same shape as `in`: in[i] is taken as 0 where mask[i] <= 0 (ReLU backward)
@@ -301,12 +303,24 @@ blur_pair_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
                 o2[0] = acc[o][0][0];
                 o2[a.qp] = acc[o][0][1];
             } else {
-                if (gy >= a.tiles_y * 4) continue;
-                const size_t item = ((size_t)np * a.tiles_y + (gy >> 2)) * a.tiles_x + blockIdx.x;
-                float4* o4 = reinterpret_cast<float4*>(out + ((item * a.Cn + cn) * 16 + (gy & 3)) * 128) + 2 * g + p;
+                // strip-major Xk: the row belongs to a full 4-row strip or to the tail strip of its cell
+                // row; gap rows (and rows beyond the mosaic) belong to no strip and are not written
+                const int rm = s_rowmap[yb * RY + o + C];
+                if (rm < 0) continue;
+                const int jy = rm >> 16, ly = rm & 0xffff, t = ly >> 2, r = ly & 3;
+                const size_t cellrow = (size_t)np * a.m.ky + jy;
+                size_t base; int rows;
+                if (t < a.sq) {
+                    rows = 4;
+                    base = (((cellrow * a.sq + t) * a.tiles_x + blockIdx.x) * a.Cn + cn) * (size_t)(16 * 128);
+                } else {
+                    rows = a.stail;
+                    base = (size_t)a.tail_base + ((cellrow * a.tiles_x + blockIdx.x) * a.Cn + cn) * (size_t)(4 * rows * 128);
+                }
+                float4* o4 = reinterpret_cast<float4*>(out + base + r * 128) + 2 * g + p;
 #pragma unroll
-                for (int k = 0; k < NOUT; ++k)               // k stride: 4 rows * 128 floats
-                    o4[k * 128] = make_float4(acc[o][k][0].x, acc[o][k][0].y, acc[o][k][1].x, acc[o][k][1].y);
+                for (int k = 0; k < NOUT; ++k)               // k stride: `rows` rows of 128 floats
+                    o4[k * rows * 32] = make_float4(acc[o][k][0].x, acc[o][k][0].y, acc[o][k][1].x, acc[o][k][1].y);
             }
         }
     }
@@ -337,7 +351,7 @@ void launch_c(const float* in, float* out, PairBlurArgs& a, int pairs_times_c, c
         if (a.mask) mmap = make_map_f32(a.mask, 3, dims, strides, box);
     }
     const int gx = MODE == 3 ? a.tiles_x : (a.W + PT_W - 1) / PT_W;
-    const int gy = MODE == 3 ? (a.tiles_y * 4 + G::TH - 1) / G::TH : (a.H + G::TH - 1) / G::TH;
+    const int gy = (a.H + G::TH - 1) / G::TH;
     for (int z0 = 0; z0 < pairs_times_c; z0 += 65535) {
         const int nz = pairs_times_c - z0 < 65535 ? pairs_times_c - z0 : 65535;
         a.z0 = z0;
@@ -398,7 +412,8 @@ void launch_blur_bank_strips(const float* in, float* out_strips, const Mosaic& m
     fill_pairs(a.fx[0], f.h0, f.kb); fill_pairs(a.fx[1], f.h1, f.kb); fill_pairs(a.fx[2], f.h2, f.kb);
     fill_pairs(a.fy[0], f.v0, f.kb); fill_pairs(a.fy[1], f.v1, f.kb); fill_pairs(a.fy[2], f.v2, f.kb);
     a.H = H; a.W = W; a.N = N; a.Cn = S; a.m = m;
-    a.tiles_x = (W + 63) / 64; a.tiles_y = (H + 3) / 4;
+    const StripGeom sg = strip_geometry(m, S);
+    a.tiles_x = sg.tiles_x; a.sq = sg.q; a.stail = sg.tail; a.tail_base = (long long)sg.tail_base_floats;
     launch_pair<3>(in, out_strips, a, f.kb, ((N + 1) / 2) * S, stream);
 }
 

@@ -43,8 +43,12 @@ namespace {
 
 using namespace tma;
 
-// lane = (lx 0..15, ly 0..1) owns an R x 4 strip of both images; R (16, 15 or 14) is picked per shape so
-// that the 2R-row tiles waste the fewest rows (28-row maps: R = 14, the 30-row mosaic of 13 x 13 maps: R = 15)
+// lane = (lx 0..15, ly 0..1) owns an R x 4 strip of both images.  Two ways to place the two strips of a tile:
+//  * stacked (ly_stride == R): the tile is 2R consecutive mosaic rows; R (16, 15 or 14) is picked per shape so
+//    that the 2R-row tiles waste the fewest rows (28-row maps: R = 14);
+//  * cell rows (ly_stride == the mosaic's row pitch, R == the image height, 13..16): ly = 0 / 1 own the rows of
+//    two consecutive CELL rows of the mosaic and nobody computes the gap rows between them (13 x 13 maps:
+//    26 rows of work per tile instead of 30)
 constexpr int C = 4, LX = 16, LY = 2, NW = 8;
 // CTA = 3 warpgroups: warpgroup 0 holds the producer lane and gives its registers away
 // (setmaxnreg.dec), warpgroups 1-2 are the 8 consumer warps and grow to CONS_REGS each.
@@ -53,19 +57,20 @@ constexpr int TW = LX * C;
 
 template <int HALO, int R>
 struct TGeom {
-    static constexpr int TH = LY * R;
+    static constexpr int TH = LY * R;                     // rows a tile computes (not its extent in cell-row mode)
     // the innermost TMA start coordinate must be 16-byte aligned: 2*(x0-HX)/4 floats -> HX % 8 == 0
     static constexpr int HX = (HALO + 7) / 8 * 8, HY = HALO;
     static constexpr int QS = (TW + 2 * HX) / 4;          // float2 per column plane
-    static constexpr int THH = TH + 2 * HY;
     static constexpr int ROW = 4 * QS;                    // float2 per tile row
-    static constexpr int TILE_BYTES = THH * ROW * 8;
 };
 
 struct TGatherParams {
     const UnitRec* table; const float* bias; float* out;
     int N, Cin, Cout, G, H, W;
     int tiles_x, nstage;
+    int ly_stride;         // mosaic rows between the strips of ly = 0 and ly = 1: R (stacked) or the cell pitch
+    int tile_pitch_y;      // mosaic rows between consecutive tiles: 2R (stacked) or two cell pitches
+    int tile_bytes;        // (ly_stride + R + 2 halo) haloed rows of the input tile
     int stage_bytes;       // tile + records, multiple of 128
     int debug;             // development switches, only with -DDAU_DEV_SWITCHES (dau_common.hpp)
     int relu;              // epilogue: store max(0, y + bias)  
@@ -83,7 +88,8 @@ __device__ __forceinline__ void build_store_maps(const TGatherParams& p, int x0,
                                                  int* s_colmap) {
     if (tid < TH + TW) {
         const bool row = tid < TH;
-        const int v = row ? y0 + tid : x0 + tid - TH;
+        constexpr int R = TH / LY;                       // row tid = strip ly = tid / R, row r = tid % R of it
+        const int v = row ? y0 + (tid / R) * p.ly_stride + tid % R : x0 + tid - TH;
         const int ext = row ? p.H : p.W, pitch = row ? p.m.py : p.m.px, size = row ? p.m.H : p.m.W,
                   cells = row ? p.m.ky : p.m.kx;
         int code = -1;
@@ -113,7 +119,7 @@ __device__ __forceinline__ void store_strip(const TGatherParams& p, const float2
         if (n >= p.N) break;
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            const int y = y0 + ly * R + r;
+            const int y = y0 + ly * p.ly_stride + r;
             if (y >= H) continue;
             float v[C];
 #pragma unroll
@@ -147,6 +153,7 @@ dau_gather_tma_kernel(const __grid_constant__ CUtensorMap in_map, const TGatherP
     using GEO = TGeom<HALO, R>;
     constexpr int TH = GEO::TH;
     constexpr int QS = GEO::QS, ROW = GEO::ROW;
+    const int TILE_BYTES = p.tile_bytes;
     extern __shared__ unsigned char smem_dyn[];
     __shared__ uint64_t full_bar[8], empty_bar[8];
     // TMA destinations must be 128-byte aligned; the dynamic segment carries 128 spare bytes
@@ -168,7 +175,7 @@ dau_gather_tma_kernel(const __grid_constant__ CUtensorMap in_map, const TGatherP
     const int tile_i = item % p.gx, cg = (item / p.gx) % p.gy;
     const int np = item / (p.gx * p.gy);       // image pair
     const int tyi = tile_i / p.tiles_x, txi = tile_i - tyi * p.tiles_x;
-    const int x0 = txi * TW, y0 = tyi * TH;
+    const int x0 = txi * TW, y0 = tyi * p.tile_pitch_y;
     const int co0 = cg * NW;
     const int nrec = min(NW, p.Cout - co0) * p.G;
     const int nstage = p.nstage;
@@ -186,14 +193,14 @@ dau_gather_tma_kernel(const __grid_constant__ CUtensorMap in_map, const TGatherP
         asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;\n" ::"n"(PROD_REGS));
         if (warp == -4 && lane == 0) {
             if (!(DAU_DEV_BITS(p.debug) & 1)) prefetch_map(&in_map);
-            const uint32_t tx_bytes = ((DAU_DEV_BITS(p.debug) & 2) ? 0 : GEO::TILE_BYTES) + ((DAU_DEV_BITS(p.debug) & 4) ? 0 : nrec * (uint32_t)sizeof(UnitRec));
+            const uint32_t tx_bytes = ((DAU_DEV_BITS(p.debug) & 2) ? 0 : TILE_BYTES) + ((DAU_DEV_BITS(p.debug) & 4) ? 0 : nrec * (uint32_t)sizeof(UnitRec));
             for (int ci = ci_begin; ci < ci_end; ++ci) {
                 const int st = (ci - ci_begin) % nstage, use = (ci - ci_begin) / nstage;
                 if (use > 0) mbar_wait_backoff(&empty_bar[st], (use - 1) & 1);
                 unsigned char* dst = smem_raw + (size_t)st * p.stage_bytes;
                 mbar_arrive_expect_tx(&full_bar[st], tx_bytes);
                 if (!(DAU_DEV_BITS(p.debug) & 2)) tensor4_g2s(dst, &in_map, 2 * ((x0 - GEO::HX) / 4), 0, y0 - GEO::HY, np * p.Cin + ci, &full_bar[st]);
-                if (!(DAU_DEV_BITS(p.debug) & 4)) bulk_g2s(dst + GEO::TILE_BYTES, p.table + ((size_t)ci * p.Cout + co0) * p.G,
+                if (!(DAU_DEV_BITS(p.debug) & 4)) bulk_g2s(dst + TILE_BYTES, p.table + ((size_t)ci * p.Cout + co0) * p.G,
                          nrec * (uint32_t)sizeof(UnitRec), &full_bar[st]);
             }
         }
@@ -211,14 +218,14 @@ dau_gather_tma_kernel(const __grid_constant__ CUtensorMap in_map, const TGatherP
 #pragma unroll
         for (int c = 0; c < C; ++c) acc[r][c] = make_float2(0.f, 0.f);
 
-    const int lane_base = ly * R * ROW + lx;
+    const int lane_base = ly * p.ly_stride * ROW + lx;
     for (int ci = ci_begin; ci < ci_end; ++ci) {
         const int st = (ci - ci_begin) % nstage, use = (ci - ci_begin) / nstage;
         mbar_wait(&full_bar[st], use & 1);
         const unsigned char* sbase = smem_raw + (size_t)st * p.stage_bytes;
         if (co_valid) {
             const float2* tile = reinterpret_cast<const float2*>(sbase) + lane_base;
-            const UnitRec* recs = reinterpret_cast<const UnitRec*>(sbase + GEO::TILE_BYTES) + warp * p.G;
+            const UnitRec* recs = reinterpret_cast<const UnitRec*>(sbase + TILE_BYTES) + warp * p.G;
             for (int g = 0; g < p.G; ++g) {
                 const float4 wv = *reinterpret_cast<const float4*>(&recs[g]);
                 const int2 off = *reinterpret_cast<const int2*>(&recs[g].offx_h);
@@ -278,7 +285,7 @@ __global__ void __launch_bounds__(NW * 32) gather_tail_kernel(const TGatherParam
     const int item = p.full_items + blockIdx.x;
     const int tile_i = item % p.gx, cg = (item / p.gx) % p.gy, np = item / (p.gx * p.gy);
     const int tyi = tile_i / p.tiles_x, txi = tile_i - tyi * p.tiles_x;
-    const int x0 = txi * TW, y0 = tyi * TH;
+    const int x0 = txi * TW, y0 = tyi * p.tile_pitch_y;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     __shared__ int s_rowmap[TH], s_colmap[TW];
     build_store_maps<TH>(p, x0, y0, tid, s_rowmap, s_colmap);
@@ -325,7 +332,6 @@ void fill_t(GatherPlan& pl) {
     using GEO = TGeom<HALO, R>;
     pl.halo_x = GEO::HX; pl.halo_y = GEO::HY;
     pl.row_stride = GEO::ROW * 2; pl.img_stride = 0;
-    pl.stage_words = GEO::TILE_BYTES / 4;
 }
 
 }  // namespace
@@ -335,14 +341,20 @@ size_t paired_layout_floats(int N, int Cn, int H, int W) {
     return (size_t)((N + 1) / 2) * Cn * H * 4 * qp * 2;
 }
 
-bool plan_gather_tma(int N, int Cin, int Cout, int G, int H, int W, int max_off, int num_sms, GatherPlan* out) {
+bool plan_gather_tma(const Mosaic& m, int Cin, int Cout, int G, int max_off, int num_sms, GatherPlan* out) {
+    const int N = m.Nv, H = m.Hv, W = m.Wv;
     int hclass = 0;
     while (kHalos[hclass] < max_off) ++hclass;
     GatherPlan pl; memset(&pl, 0, sizeof(pl));
     pl.kind = 1; pl.variant = hclass;
-    // strip rows R: the 2R-row tiling that computes the fewest rows (ties: the taller strip)
+    // strip rows R.  Cell-row mode when the mosaic stacks cells of 13..16 rows: R = the image height, the two
+    // strips of a tile sit one cell pitch apart.  Else stacked strips: the 2R-row tiling that computes the
+    // fewest rows (ties: the taller strip).
     int R = 16;
-    {
+    const bool cell_rows = m.ky >= 2 && m.H >= 13 && m.H <= 16;
+    if (cell_rows) {
+        R = m.H;
+    } else {
         long best = -1;
         for (int r : {16, 15, 14}) {
             const long rows = (long)((H + 2 * r - 1) / (2 * r)) * 2 * r;
@@ -351,11 +363,14 @@ bool plan_gather_tma(int N, int Cin, int Cout, int G, int H, int W, int max_off,
     }
     const int TH = LY * R;
     pl.tile_w = TW; pl.tile_h = TH; pl.imgs = 2; pl.cout_per_cta = NW;
+    pl.ly_stride = cell_rows ? m.py : R;
+    pl.tile_pitch_y = cell_rows ? 2 * m.py : TH;
 #define DAU_FILL(HALO)                                              \
     switch (R) {                                                    \
         case 16: fill_t<HALO, 16>(pl); break;                       \
         case 15: fill_t<HALO, 15>(pl); break;                       \
-        default: fill_t<HALO, 14>(pl); break;                       \
+        case 14: fill_t<HALO, 14>(pl); break;                       \
+        default: fill_t<HALO, 13>(pl); break;                       \
     }
     switch (hclass) {
         case 0: DAU_FILL(4); break;
@@ -364,7 +379,9 @@ bool plan_gather_tma(int N, int Cin, int Cout, int G, int H, int W, int max_off,
         default: DAU_FILL(32); break;
     }
 #undef DAU_FILL
-    const size_t tile_bytes = (size_t)pl.stage_words * 4;
+    pl.tile_rows = pl.ly_stride + R + 2 * pl.halo_y;
+    const size_t tile_bytes = (size_t)pl.tile_rows * (pl.row_stride / 2) * 8;      // rows x ROW float2
+    pl.tile_bytes = (int)tile_bytes;
     const size_t stage = (tile_bytes + (size_t)NW * G * sizeof(UnitRec) + 127) / 128 * 128;
     int nstage = (int)((200 * 1024 - 128) / stage);
     if (nstage > 4) nstage = 4;
@@ -372,7 +389,8 @@ bool plan_gather_tma(int N, int Cin, int Cout, int G, int H, int W, int max_off,
     pl.stage_words = (int)(stage / 4);
     pl.nstage = nstage;
     pl.smem_bytes = stage * nstage + 128;
-    pl.grid_x = ((W + TW - 1) / TW) * ((H + TH - 1) / TH);
+    const int tiles_y = cell_rows ? (m.ky + 1) / 2 : (H + TH - 1) / TH;
+    pl.grid_x = ((W + TW - 1) / TW) * tiles_y;
     pl.grid_y = (Cout + NW - 1) / NW;
     pl.grid_z = (N + 1) / 2;
     // One CTA per SM: `items` equal CTAs take ceil(items / SMs) rounds.  The items of the last,
@@ -408,14 +426,14 @@ void launch_gather_tma(const GatherPlan& plan, const float* in_paired, const Uni
     const uint64_t dims[4] = {2 * qv, 4, (uint64_t)H, (uint64_t)((N + 1) / 2) * Cin};
     const uint64_t strides[3] = {qp * 8, 4 * qp * 8, (uint64_t)H * 4 * qp * 8};
     const int halo_q2 = 2 * ((TW + 2 * plan.halo_x) / 4);
-    const int TH = plan.tile_h;
-    const uint32_t box[4] = {(uint32_t)halo_q2, 4, (uint32_t)(TH + 2 * plan.halo_y), 1};
+    const uint32_t box[4] = {(uint32_t)halo_q2, 4, (uint32_t)plan.tile_rows, 1};
     const CUtensorMap map = make_map_f32(in_paired, 4, dims, strides, box);
     TGatherParams p;
     p.table = table; p.bias = bias; p.out = out;
     p.N = N; p.Cin = Cin; p.Cout = Cout; p.G = G; p.H = H; p.W = W;
     p.tiles_x = (W + TW - 1) / TW; p.nstage = plan.nstage;
     p.stage_bytes = plan.stage_words * 4;
+    p.ly_stride = plan.ly_stride; p.tile_pitch_y = plan.tile_pitch_y; p.tile_bytes = plan.tile_bytes;
     p.m = m; p.relu = relu; p.crop = crop;
     p.gx = plan.grid_x; p.gy = plan.grid_y; p.full_items = plan.full_items; p.split_k = plan.split_k;
     p.part = reinterpret_cast<float2*>(part_buf);
@@ -428,7 +446,8 @@ void launch_gather_tma(const GatherPlan& plan, const float* in_paired, const Uni
     switch (plan.tile_h / LY) {                                              \
         case 16: launch_t<HALO, 16>(plan, map, p, stream); break;            \
         case 15: launch_t<HALO, 15>(plan, map, p, stream); break;            \
-        default: launch_t<HALO, 14>(plan, map, p, stream); break;            \
+        case 14: launch_t<HALO, 14>(plan, map, p, stream); break;            \
+        default: launch_t<HALO, 13>(plan, map, p, stream); break;            \
     }
     switch (plan.variant) {
         case 0: DAU_LAUNCH(4); break;

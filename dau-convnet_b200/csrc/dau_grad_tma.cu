@@ -22,9 +22,14 @@
 //
 // How operands move and how the FMAs are packed:
 //
-//  * work item = (image PAIR, 4-row x 64-column tile).  Everything is laid out so that the two
-//    images of a pair are the two halves of one fma.rn.f32x2 (SASS FFMA2) operand: they share the
-//    unit's offsets and bilinear weights, so no register shuffling is ever needed to form pairs;
+//  * work item = (image PAIR, row strip, 64-column tile).  Row strips never contain a mosaic gap row:
+//    every cell row of the mosaic is cut into H/4 full strips of 4 rows and one tail strip of H%4
+//    rows (StripGeom in dau_kernels.cuh); the kernel walks its full items with the 4-row code and
+//    then its tail items with a copy of the same code instantiated for the tail height, so a 13-row
+//    map costs 13 rows of work and not the 16 of four 4-row tiles (or the 32 of eight mosaic tiles
+//    for 26 rows, as before).  Everything is laid out so that the two images of a pair are the two
+//    halves of one fma.rn.f32x2 (SASS FFMA2) operand: they share the unit's offsets and bilinear
+//    weights, so no register shuffling is ever needed to form pairs;
 //  * the derivative-blur kernel writes Xk "strip-major":
 //        XS[item][s][k][r<4][lane<32][c<2][img<2]
 //    so that everything the 8 consumer warps (= 8 input channels) of a CTA need for one item is
@@ -62,7 +67,8 @@ constexpr int R = 4, C = 2, NW = 8, UPW = 12, TW = 64, TH = 4;
 // (setmaxnreg.dec), warpgroups 1-2 are the 8 consumer warps and grow to CONS_REGS each
 // (setmaxnreg.inc): every SM sub-partition then holds 1 x PROD_REGS + 2 x CONS_REGS <= 512 per lane.
 constexpr int NTHREADS = (NW + 4) * 32, PROD_REGS = 40, CONS_REGS = 232;
-constexpr int XK_WARP_BYTES = 4 * R * 32 * C * 2 * 4;  // 8 KB: [k][r][lane][c][img]
+constexpr int XK_ROW_BYTES = 32 * C * 2 * 4;            // one (k, r) row of a warp's strip: 512 B
+constexpr int XK_WARP_BYTES = 4 * R * XK_ROW_BYTES;     // 8 KB: [k][r][lane][c][img] of a full strip
 
 template <int HALO>
 struct GGeomT {
@@ -85,17 +91,100 @@ struct TGradParams {
     const float* xs; const UnitRec* table; float* partial;
     int N, S, F, G;
     int FC, GC, n_gchunks;
-    int tiles_x, tiles, items, items_per_split;
+    int tiles_x, ky, py, q;            // strip geometry (StripGeom)
+    long long full_items, tail_items;
+    long long full_per_split, tail_per_split;
+    long long tail_base_floats;
     int feat_bytes_al;     // FEAT_BYTES rounded up to 128
     int stage_bytes;
-    int debug;             // DAU_DEBUG bits (development): 2 skip error tiles, 4 skip Xk copy, 8 skip the math
+    int debug;             // development switches, only with -DDAU_DEV_SWITCHES (dau_common.hpp)
 };
 
-template <int HALO>
+// (pair, first mosaic row, column tile) of a full (tail == false) or tail item
+__device__ __forceinline__ void item_origin(const TGradParams& p, long long item, bool tail, int* np, int* y0, int* txi) {
+    const int tx = (int)(item % p.tiles_x);
+    long long v = item / p.tiles_x;
+    int t = p.q;
+    if (!tail) { t = (int)(v % p.q); v /= p.q; }
+    const int jy = (int)(v % p.ky);
+    *np = (int)(v / p.ky); *y0 = jy * p.py + 4 * t; *txi = tx;
+}
+
+// One item of a consumer warp: its Xk strip (RR rows) to registers, then the walk over the units.
+template <int HALO, int RR>
+__device__ __forceinline__ void consume_item(const unsigned char* smem_raw, const TGradParams& p, const GUnit* units,
+                                             float2 (&acc)[UPW][4], int warp, int lane, bool s_valid, int kk,
+                                             uint64_t* xfull_bar, uint64_t* xempty_bar, uint64_t* full_bar,
+                                             uint64_t* empty_bar) {
+    using GEO = GGeomT<HALO>;
+    constexpr int QS = GEO::QS, ROW = GEO::ROW;
+    const int st = kk & 1, use = kk >> 1;
+    float2 xk[4][RR][C];
+    mbar_wait(xfull_bar, kk & 1);
+    if (s_valid) {
+        const float4* xsrc = reinterpret_cast<const float4*>(smem_raw + 2 * (size_t)p.stage_bytes +
+                                                             warp * (4 * RR * XK_ROW_BYTES)) + lane;
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+#pragma unroll
+            for (int r = 0; r < RR; ++r) {
+                const float4 v = xsrc[(k * RR + r) * 32];
+                xk[k][r][0] = make_float2(v.x, v.y);
+                xk[k][r][1] = make_float2(v.z, v.w);
+            }
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(xempty_bar);               // the buffer may be refilled while we compute
+    mbar_wait(&full_bar[st], use & 1);
+    const unsigned char* sbase = smem_raw + (size_t)st * p.stage_bytes;
+    if (s_valid && !(DAU_DEV_BITS(p.debug) & 8)) {
+        const float2* tb = reinterpret_cast<const float2*>(sbase) + lane;
+#pragma unroll
+        for (int u = 0; u < UPW; ++u) {
+            const GUnit* rec = &units[u];
+            const float4 wa = *reinterpret_cast<const float4*>(&rec->w00);   // w00 w00 w01 w01
+            const float4 wb = *reinterpret_cast<const float4*>(&rec->w10);   // w10 w10 w11 w11
+            const int4 off = *reinterpret_cast<const int4*>(&rec->offx);     // offx, offy, tile offset
+            const float2 w00 = make_float2(wa.x, wa.y), w01 = make_float2(wa.z, wa.w);
+            const float2 w10 = make_float2(wb.x, wb.y), w11 = make_float2(wb.z, wb.w);
+            const int b = off.x & 1;
+            const float2* base = tb + off.z + off.y * ROW + (off.x >> 1);
+            const float2* colp[C + 1];
+#pragma unroll
+            for (int c = 0; c <= C; ++c) {
+                const int m = b + c;
+                colp[c] = base + (m & 1) * QS + (m >> 1);
+            }
+            float2 prev[C + 1];
+#pragma unroll
+            for (int c = 0; c <= C; ++c) prev[c] = colp[c][0];
+#pragma unroll
+            for (int r = 1; r <= RR; ++r) {
+                float2 cur[C + 1];
+#pragma unroll
+                for (int c = 0; c <= C; ++c) cur[c] = colp[c][r * ROW];
+#pragma unroll
+                for (int c = 0; c < C; ++c) {
+                    float2 e = __fmul2_rn(w00, prev[c]);
+                    e = __ffma2_rn(w01, prev[c + 1], e);
+                    e = __ffma2_rn(w10, cur[c], e);
+                    e = __ffma2_rn(w11, cur[c + 1], e);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) acc[u][k] = __ffma2_rn(e, xk[k][r - 1][c], acc[u][k]);
+                }
+#pragma unroll
+                for (int c = 0; c <= C; ++c) prev[c] = cur[c];
+            }
+        }
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&empty_bar[st]);
+}
+
+template <int HALO, int TAIL>
 __global__ void __launch_bounds__(NTHREADS, 1)
 dau_grad_tma_kernel(const __grid_constant__ CUtensorMap err_map, const TGradParams p) {
     using GEO = GGeomT<HALO>;
-    constexpr int QS = GEO::QS, ROW = GEO::ROW;
     extern __shared__ unsigned char smem_dyn[];
     __shared__ uint64_t full_bar[2], empty_bar[2];      // error-tile ring
     __shared__ uint64_t xfull_bar, xempty_bar;           // the single Xk buffer
@@ -112,8 +201,12 @@ dau_grad_tma_kernel(const __grid_constant__ CUtensorMap err_map, const TGradPara
     const int nfeat = min(p.FC, F - f0), ngc = min(p.GC, G - g0);
     const int nunits = nfeat * ngc;
     const int nsv = min(NW, p.S - s0);                 // valid input channels of this CTA
-    const int item_begin = blockIdx.z * p.items_per_split;
-    const int item_end = min(p.items, item_begin + p.items_per_split);
+    // this CTA's share of the reduction axis: a range of full items, then a range of tail items
+    const long long fb = min(p.full_items, (long long)blockIdx.z * p.full_per_split);
+    const long long fe = min(p.full_items, fb + p.full_per_split);
+    const long long tb_ = TAIL ? min(p.tail_items, (long long)blockIdx.z * p.tail_per_split) : 0;
+    const long long te = TAIL ? min(p.tail_items, tb_ + p.tail_per_split) : 0;
+    const int nfull = (int)(fe - fb), nsteps = nfull + (int)(te - tb_);
 
     if (tid == 0) {
         for (int s = 0; s < 2; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], NW); }
@@ -122,7 +215,7 @@ dau_grad_tma_kernel(const __grid_constant__ CUtensorMap err_map, const TGradPara
     }
     if (warp >= 0 && lane < UPW) {
         // slots beyond the chunk's units are dummies (zero weights, in-tile offsets): the unit loop
-        // below is branch-free so that one unit's prologue overlaps the previous unit's math
+        // is branch-free so that one unit's prologue overlaps the previous unit's math
         GUnit gu;
         gu.w00 = gu.w01 = gu.w10 = gu.w11 = make_float2(0.f, 0.f);
         gu.offx = GEO::HX; gu.offy = GEO::HY; gu.tile_off = 0; gu.pad = 0;
@@ -143,24 +236,28 @@ dau_grad_tma_kernel(const __grid_constant__ CUtensorMap err_map, const TGradPara
         if (warp == -4 && lane == 0) {
             prefetch_map(&err_map);
             // Error tiles go through a 2-stage ring.  Xk needs ONE buffer only: the consumers move it
-            // to registers at the start of an item, so the next item's 64 KB copy overlaps the math.
+            // to registers at the start of an item, so the next item's copy overlaps the math.
             const uint32_t tx_e = (DAU_DEV_BITS(p.debug) & 2) ? 0 : nfeat * GEO::FEAT_BYTES;
-            const uint32_t tx_x = (DAU_DEV_BITS(p.debug) & 4) ? 0 : nsv * XK_WARP_BYTES;
             unsigned char* xdst = smem_raw + 2 * (size_t)p.stage_bytes;
-            for (int item = item_begin; item < item_end; ++item) {
-                const int k = item - item_begin, st = k & 1, use = k >> 1;
-                const int n = item / p.tiles, t = item - n * p.tiles;   // n = image pair
-                const int tyi = t / p.tiles_x, txi = t - tyi * p.tiles_x;
+            for (int k = 0; k < nsteps; ++k) {
+                const bool tail = k >= nfull;
+                const long long item = tail ? tb_ + (k - nfull) : fb + k;
+                const int st = k & 1, use = k >> 1;
+                int n, y0, txi;                                       // n = image pair
+                item_origin(p, item, tail, &n, &y0, &txi);
+                const uint32_t xbytes = (tail ? TAIL : R) * 4 * XK_ROW_BYTES;      // per input channel
+                const float* xsrc = tail ? p.xs + p.tail_base_floats + ((size_t)item * p.S + s0) * (xbytes / 4)
+                                         : p.xs + ((size_t)item * p.S + s0) * (XK_WARP_BYTES / 4);
                 if (k > 0) mbar_wait_backoff(&xempty_bar, (k - 1) & 1);
+                const uint32_t tx_x = (DAU_DEV_BITS(p.debug) & 4) ? 0 : nsv * xbytes;
                 mbar_arrive_expect_tx(&xfull_bar, tx_x);
-                if (!(DAU_DEV_BITS(p.debug) & 4)) bulk_g2s(xdst, p.xs + ((size_t)item * p.S + s0) * (XK_WARP_BYTES / 4),
-                                             nsv * XK_WARP_BYTES, &xfull_bar);
+                if (!(DAU_DEV_BITS(p.debug) & 4)) bulk_g2s(xdst, xsrc, nsv * xbytes, &xfull_bar);
                 if (use > 0) mbar_wait_backoff(&empty_bar[st], (use - 1) & 1);
                 unsigned char* dst = smem_raw + (size_t)st * p.stage_bytes;
                 mbar_arrive_expect_tx(&full_bar[st], tx_e);
                 for (int fi = 0; fi < nfeat && !(DAU_DEV_BITS(p.debug) & 2); ++fi)
                     tensor4_g2s(dst + fi * p.feat_bytes_al, &err_map, txi * TW - GEO::HX, 0,
-                                tyi * TH - GEO::HY, n * F + f0 + fi, &full_bar[st]);
+                                y0 - GEO::HY, n * F + f0 + fi, &full_bar[st]);
             }
         }
         return;
@@ -175,68 +272,13 @@ dau_grad_tma_kernel(const __grid_constant__ CUtensorMap err_map, const TGradPara
 #pragma unroll
         for (int k = 0; k < 4; ++k) acc[u][k] = make_float2(0.f, 0.f);
 
-    for (int item = item_begin; item < item_end; ++item) {
-        const int kk = item - item_begin, st = kk & 1, use = kk >> 1;
-        float2 xk[4][R][C];
-        mbar_wait(&xfull_bar, kk & 1);
-        if (s_valid) {
-            const float4* xsrc = reinterpret_cast<const float4*>(smem_raw + 2 * (size_t)p.stage_bytes +
-                                                                 warp * XK_WARP_BYTES) + lane;
-#pragma unroll
-            for (int k = 0; k < 4; ++k)
-#pragma unroll
-                for (int r = 0; r < R; ++r) {
-                    const float4 v = xsrc[(k * R + r) * 32];
-                    xk[k][r][0] = make_float2(v.x, v.y);
-                    xk[k][r][1] = make_float2(v.z, v.w);
-                }
-        }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&xempty_bar);           // the buffer may be refilled while we compute
-        mbar_wait(&full_bar[st], use & 1);
-        const unsigned char* sbase = smem_raw + (size_t)st * p.stage_bytes;
-        if (s_valid && !(DAU_DEV_BITS(p.debug) & 8)) {
-            const float2* tb = reinterpret_cast<const float2*>(sbase) + lane;
-#pragma unroll
-            for (int u = 0; u < UPW; ++u) {
-                const GUnit* rec = &s_units[warp][u];
-                const float4 wa = *reinterpret_cast<const float4*>(&rec->w00);   // w00 w00 w01 w01
-                const float4 wb = *reinterpret_cast<const float4*>(&rec->w10);   // w10 w10 w11 w11
-                const int4 off = *reinterpret_cast<const int4*>(&rec->offx);     // offx, offy, tile offset
-                const float2 w00 = make_float2(wa.x, wa.y), w01 = make_float2(wa.z, wa.w);
-                const float2 w10 = make_float2(wb.x, wb.y), w11 = make_float2(wb.z, wb.w);
-                const int b = off.x & 1;
-                const float2* base = tb + off.z + off.y * ROW + (off.x >> 1);
-                const float2* colp[C + 1];
-#pragma unroll
-                for (int c = 0; c <= C; ++c) {
-                    const int m = b + c;
-                    colp[c] = base + (m & 1) * QS + (m >> 1);
-                }
-                float2 prev[C + 1];
-#pragma unroll
-                for (int c = 0; c <= C; ++c) prev[c] = colp[c][0];
-#pragma unroll
-                for (int r = 1; r <= R; ++r) {
-                    float2 cur[C + 1];
-#pragma unroll
-                    for (int c = 0; c <= C; ++c) cur[c] = colp[c][r * ROW];
-#pragma unroll
-                    for (int c = 0; c < C; ++c) {
-                        float2 e = __fmul2_rn(w00, prev[c]);
-                        e = __ffma2_rn(w01, prev[c + 1], e);
-                        e = __ffma2_rn(w10, cur[c], e);
-                        e = __ffma2_rn(w11, cur[c + 1], e);
-#pragma unroll
-                        for (int k = 0; k < 4; ++k) acc[u][k] = __ffma2_rn(e, xk[k][r - 1][c], acc[u][k]);
-                    }
-#pragma unroll
-                    for (int c = 0; c <= C; ++c) prev[c] = cur[c];
-                }
-            }
-        }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&empty_bar[st]);
+    for (int kk = 0; kk < nfull; ++kk)
+        consume_item<HALO, R>(smem_raw, p, s_units[warp], acc, warp, lane, s_valid, kk, &xfull_bar, &xempty_bar,
+                              full_bar, empty_bar);
+    if (TAIL > 0) {
+        for (int kk = nfull; kk < nsteps; ++kk)
+            consume_item<HALO, (TAIL > 0 ? TAIL : 1)>(smem_raw, p, s_units[warp], acc, warp, lane, s_valid, kk,
+                                                      &xfull_bar, &xempty_bar, full_bar, empty_bar);
     }
 
     if (s_valid) {
@@ -262,16 +304,26 @@ dau_grad_tma_kernel(const __grid_constant__ CUtensorMap err_map, const TGradPara
 
 constexpr int kHalos[4] = {4, 8, 16, 32};
 
-template <int HALO>
+template <int HALO, int TAIL>
 void launch_t(const GradPlan& plan, const CUtensorMap& map, const TGradParams& p, cudaStream_t stream) {
     static PerDeviceOnce once;                 // the attribute is per (kernel, device)
     if (once.need()) {
-        DAU_CUDA_CHECK(cudaFuncSetAttribute(dau_grad_tma_kernel<HALO>,
+        DAU_CUDA_CHECK(cudaFuncSetAttribute(dau_grad_tma_kernel<HALO, TAIL>,
                                             cudaFuncAttributeMaxDynamicSharedMemorySize, 221 * 1024));
         once.done();
     }
     dim3 grid(plan.grid_x, plan.grid_y, plan.grid_z);
-    dau_grad_tma_kernel<HALO><<<grid, NTHREADS, plan.smem_bytes, stream>>>(map, p);
+    dau_grad_tma_kernel<HALO, TAIL><<<grid, NTHREADS, plan.smem_bytes, stream>>>(map, p);
+}
+
+template <int HALO>
+void launch_h(const GradPlan& plan, const CUtensorMap& map, const TGradParams& p, cudaStream_t stream) {
+    switch (plan.tail) {
+        case 0: launch_t<HALO, 0>(plan, map, p, stream); break;
+        case 1: launch_t<HALO, 1>(plan, map, p, stream); break;
+        case 2: launch_t<HALO, 2>(plan, map, p, stream); break;
+        default: launch_t<HALO, 3>(plan, map, p, stream); break;
+    }
 }
 
 template <int HALO>
@@ -285,16 +337,25 @@ void fill_t(GradPlan& pl) {
 }  // namespace
 
 // ---- layouts -------------------------------------------------------------------------------------
-size_t strip_layout_floats(int N, int S, int H, int W) {
-    const size_t items = (size_t)((N + 1) / 2) * ((H + TH - 1) / TH) * ((W + TW - 1) / TW);
-    return items * S * (XK_WARP_BYTES / 4);
+StripGeom strip_geometry(const Mosaic& m, int S) {
+    StripGeom g;
+    g.tiles_x = (m.Wv + TW - 1) / TW;
+    g.ky = m.ky; g.py = m.py; g.H = m.H;
+    g.q = m.H / R; g.tail = m.H % R;
+    g.pairs = (m.Nv + 1) / 2;
+    const long long cell_rows = (long long)g.pairs * g.ky * g.tiles_x;
+    g.full_items = cell_rows * g.q;
+    g.tail_items = g.tail ? cell_rows : 0;
+    g.tail_base_floats = (size_t)g.full_items * S * (XK_WARP_BYTES / 4);
+    g.total_floats = g.tail_base_floats + (size_t)g.tail_items * S * (g.tail * 4 * XK_ROW_BYTES / 4);
+    return g;
 }
 size_t error_layout_floats(int N, int F, int H, int W) {
     const size_t qv = (W + 1) / 2, qp = (qv + 1) / 2 * 2;
     return (size_t)((N + 1) / 2) * F * H * 2 * qp * 2;
 }
 
-bool plan_grad_tma(int N, int S, int F, int G, int H, int W, int max_off, int num_sms, GradPlan* out) {
+bool plan_grad_tma(const Mosaic& m, int S, int F, int G, int max_off, int num_sms, GradPlan* out) {
     int hclass = 0;
     while (kHalos[hclass] < max_off) ++hclass;
     GradPlan pl; memset(&pl, 0, sizeof(pl));
@@ -316,19 +377,23 @@ bool plan_grad_tma(int N, int S, int F, int G, int H, int W, int max_off, int nu
     pl.units_per_warp = fc * pl.g_chunk;
     const size_t stage = (size_t)fc * pl.feat_stride * 4;     // error tiles of one ring stage
     pl.smem_bytes = 2 * stage + xk_bytes + 128;
-    const long tx = (W + TW - 1) / TW, ty = (H + TH - 1) / TH;
-    const long items = tx * ty * ((N + 1) / 2);
+    const StripGeom sg = strip_geometry(m, S);
+    pl.tail = sg.tail;
     const int n_fchunks = (F + fc - 1) / fc, n_gchunks = (G + pl.g_chunk - 1) / pl.g_chunk;
     pl.grid_x = n_fchunks * n_gchunks;
     pl.grid_y = (S + NW - 1) / NW;
     if (pl.grid_y > 65535) return false;
+    // CTAs along the reduction axis: each takes ceil(full / sp) full and ceil(tail / sp) tail items; the cost of
+    // a split is counted in strip rows, the score is the fraction of the SM-rounds spent on real rows
     const long base = (long)pl.grid_x * pl.grid_y;
+    const double work = (double)sg.full_items * R + (double)sg.tail_items * sg.tail;
+    const long long most = sg.full_items > sg.tail_items ? sg.full_items : sg.tail_items;
     int best_split = 1; double best_eff = -1.0;
-    const int max_split = (int)(items < 64 ? items : 64);
+    const int max_split = (int)(most < 64 ? (most < 1 ? 1 : most) : 64);
     for (int sp = 1; sp <= max_split; ++sp) {
-        const long per = (items + sp - 1) / sp;
+        const double per = (double)((sg.full_items + sp - 1) / sp) * R + (double)((sg.tail_items + sp - 1) / sp) * sg.tail;
         const long waves = (base * sp + num_sms - 1) / num_sms;
-        const double eff = (double)(base * items) / ((double)waves * num_sms * per) - 0.002 * sp;
+        const double eff = (double)base * work / ((double)waves * num_sms * per) - 0.002 * sp;
         if (eff > best_eff + 1e-9) { best_eff = eff; best_split = sp; }
     }
     pl.n_splits = best_split; pl.grid_z = best_split;
@@ -338,32 +403,36 @@ bool plan_grad_tma(int N, int S, int F, int G, int H, int W, int max_off, int nu
 }
 
 void launch_grad_tma(const GradPlan& plan, const float* xk_strips, const float* err_sg, const UnitRec* table,
-                     float* partial, int N, int S, int F, int G, int H, int W, cudaStream_t stream) {
+                     float* partial, const Mosaic& m, int S, int F, int G, cudaStream_t stream) {
+    const int N = m.Nv, H = m.Hv, W = m.Wv;
     // tensor map of SGP[n/2][f][y][x%2][x/2][n%2]: dims (q*2+img, plane, y, (pair, f))
     const uint64_t qv = (W + 1) / 2, qp = (qv + 1) / 2 * 2;
     const uint64_t dims[4] = {2 * qv, 2, (uint64_t)H, (uint64_t)((N + 1) / 2) * F};
     const uint64_t strides[3] = {qp * 8, 2 * qp * 8, (uint64_t)H * 2 * qp * 8};
     const uint32_t box[4] = {(uint32_t)(TW + 2 * plan.halo_x), 2, (uint32_t)(TH + 2 * plan.halo_y), 1};
     const CUtensorMap map = make_map_f32(err_sg, 4, dims, strides, box);
+    const StripGeom sg = strip_geometry(m, S);
     TGradParams p;
     p.xs = xk_strips; p.table = table; p.partial = partial;
     p.N = N; p.S = S; p.F = F; p.G = G;
     p.FC = plan.feats_per_cta; p.GC = plan.g_chunk; p.n_gchunks = (G + p.GC - 1) / p.GC;
-    p.tiles_x = (W + TW - 1) / TW;
-    p.tiles = p.tiles_x * ((H + TH - 1) / TH);
-    p.items = p.tiles * ((N + 1) / 2);
-    p.items_per_split = (p.items + plan.n_splits - 1) / plan.n_splits;
+    p.tiles_x = sg.tiles_x; p.ky = sg.ky; p.py = sg.py; p.q = sg.q;
+    p.full_items = sg.full_items; p.tail_items = sg.tail_items;
+    p.full_per_split = (sg.full_items + plan.n_splits - 1) / plan.n_splits;
+    p.tail_per_split = (sg.tail_items + plan.n_splits - 1) / plan.n_splits;
+    p.tail_base_floats = (long long)sg.tail_base_floats;
     p.feat_bytes_al = plan.feat_stride * 4;
     p.stage_bytes = plan.feats_per_cta * plan.feat_stride * 4;
     p.debug = 0;
 #ifdef DAU_DEV_SWITCHES
     p.debug = getenv("DAU_DEBUG_GRAD") ? atoi(getenv("DAU_DEBUG_GRAD")) : 0;
 #endif
+    DAU_CHECK(plan.tail == sg.tail, 3, "gradient plan was made for another shape");
     switch (plan.variant) {
-        case 0: launch_t<4>(plan, map, p, stream); break;
-        case 1: launch_t<8>(plan, map, p, stream); break;
-        case 2: launch_t<16>(plan, map, p, stream); break;
-        default: launch_t<32>(plan, map, p, stream); break;
+        case 0: launch_h<4>(plan, map, p, stream); break;
+        case 1: launch_h<8>(plan, map, p, stream); break;
+        case 2: launch_h<16>(plan, map, p, stream); break;
+        default: launch_h<32>(plan, map, p, stream); break;
     }
     DAU_CUDA_CHECK(cudaGetLastError());
 }

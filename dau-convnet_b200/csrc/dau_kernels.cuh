@@ -75,6 +75,8 @@ struct GatherPlan {            // chosen once per shape by plan_gather_tma()
     int nstage;                // pipeline depth
     int variant;               // index into the instantiated tile shapes
     int tile_w, tile_h, imgs;  // output tile of one CTA: imgs x tile_h x tile_w
+    int ly_stride, tile_pitch_y;   // rows between the two strips of a tile / between tiles (see dau_gather_tma.cu)
+    int tile_rows, tile_bytes;     // haloed input tile in shared memory
     int halo_x, halo_y;
     int row_stride, img_stride;// shared-memory strides in words (bank-conflict padded)
     int stage_words;           // words per pipeline stage (tile + unit records)
@@ -92,7 +94,7 @@ struct GatherPlan {            // chosen once per shape by plan_gather_tma()
 // (N, H, W below are the MOSAIC extents m.Nv, m.Hv, m.Wv; `in` / `out` of the producers and of
 // the gather's store are the caller's real NCHW tensors)
 size_t paired_layout_floats(int N, int Cn, int H, int W);
-bool plan_gather_tma(int N, int Cin, int Cout, int G, int H, int W, int max_off, int num_sms, GatherPlan* out);
+bool plan_gather_tma(const Mosaic& m, int Cin, int Cout, int G, int max_off, int num_sms, GatherPlan* out);
 void launch_gather_tma(const GatherPlan& p, const float* in_paired, const UnitRec* table, const float* bias,
                        float* out, const Mosaic& m, int Cin, int Cout, int G, cudaStream_t stream, int relu = 0,
                        int crop = 0, float* part_buf = nullptr);
@@ -120,20 +122,35 @@ struct GradPlan {
     int units_per_warp;        // FC * G  (<= 16)
     int g_chunk;               // units of one (s,f) handled per pass (G or 16)
     int n_splits;              // CTAs along the (image,tile) reduction axis
+    int tail;                  // rows of the tail strips (H % 4): selects the kernel instantiation
     size_t smem_bytes;
     int grid_x, grid_y, grid_z;
     size_t partial_floats;     // n_splits * 4 * S*G*F
 };
 // partial[split][k][s][g][f] = sum over the split's (n,y,x) of  xk[n,s,k] * gather(err[n,f])
 
-// TMA variant: Xk in the strip-major layout XS[item][s][k][r][lane][c][img] (launch_blur_bank_strips),
-// the error in the de-interleaved pair layout SGP[n/2][f][y][x%2][x/2][n%2] with the edge mask applied
-// (launch_error_relayout)
-size_t strip_layout_floats(int N, int S, int H, int W);
+// Row strips of the gradient kernel.  Every cell row of the mosaic (m.ky of them; 1 for wide images) is
+// cut into q = H / 4 full strips of 4 rows and, when H % 4 != 0, ONE tail strip of tail = H % 4 rows;
+// the gap rows between cells belong to no strip, so no lane of the gradient kernel ever sits on a gap
+// ROW (13-row maps: 13 of 13 rows are work instead of 26 of the 32 rows of eight 4-row mosaic tiles).
+// A work item is one strip x one 64-column tile x one image pair.  XS, the strip-major Xk layout the
+// derivative-blur kernel writes and the gradient kernel copies with one cp.async.bulk per item:
+//     full items: XS[item][s][k<4][r<4][lane<32][c<2][img<2],  item = ((pair*ky + jy)*q + t)*tiles_x + tx
+//     tail items: XS[tail_base + ...][titem][s][k<4][r<tail][lane][c][img], titem = (pair*ky + jy)*tiles_x + tx
+struct StripGeom {
+    int tiles_x, ky, py, H, q, tail, pairs;
+    long long full_items, tail_items;
+    size_t tail_base_floats;         // where the tail blocks start in XS
+    size_t total_floats;
+};
+StripGeom strip_geometry(const Mosaic& m, int S);
+
+// TMA variant: Xk in the strip-major layout XS (launch_blur_bank_strips), the error in the de-interleaved
+// pair layout SGP[n/2][f][y][x%2][x/2][n%2] with the edge mask applied (launch_error_relayout)
 size_t error_layout_floats(int N, int F, int H, int W);
-bool plan_grad_tma(int N, int S, int F, int G, int H, int W, int max_off, int num_sms, GradPlan* out);
+bool plan_grad_tma(const Mosaic& m, int S, int F, int G, int max_off, int num_sms, GradPlan* out);
 void launch_grad_tma(const GradPlan& p, const float* xk_strips, const float* err_sg, const UnitRec* table,
-                     float* partial, int N, int S, int F, int G, int H, int W, cudaStream_t stream);
+                     float* partial, const Mosaic& m, int S, int F, int G, cudaStream_t stream);
 void launch_blur_bank_strips(const float* in, float* out_strips, const Mosaic& m, int S,
                              const BlurFactors& f, cudaStream_t stream);
 void launch_error_relayout(const float* err, float* out_sg, const Mosaic& m, int F, int mask_row, int mask_col,

@@ -45,11 +45,13 @@ Mosaic plan_mosaic(int N, int H, int W, int gap) {
             if (cells > 1 && 2 * cells > N) continue;          // never pad the batch by more than a pair
             const int Nv = (N + cells - 1) / cells, pairs = (Nv + 1) / 2;
             const double ex = (double)kx * W / (64.0 * ((Wv + 63) / 64));
-            // half of the flops run on the gathers' tiles (32, 30 or 28 rows, whichever wastes the
-            // fewest: plan_gather_tma), half on 4-row tiles (gradients)
+            // half of the flops run on the gathers' tiles (32, 30 or 28 consecutive rows, whichever wastes the
+            // fewest, or -- cells of 13..16 rows stacked in y -- pairs of cell rows: plan_gather_tma), half on
+            // the gradient kernel's row strips, which skip the gap rows altogether (strip_geometry)
             int grows = 1 << 30;
             for (int th : {32, 30, 28}) grows = std::min(grows, (Hv + th - 1) / th * th);
-            const double ey = 0.5 * (double)ky * H / grows + 0.5 * (double)ky * H / (4.0 * ((Hv + 3) / 4));
+            if (ky >= 2 && H >= 13 && H <= 16) grows = (ky + 1) / 2 * 2 * H;
+            const double ey = 0.5 * (double)ky * H / grows + 0.5;
             const double eb = (double)N / ((double)pairs * 2 * cells);
             const double score = ex * ey * eb - 1e-3 * cells;
             if (score > best_score + 1e-12) {
@@ -127,9 +129,9 @@ void DAUConvLayerB200::Reshape(int N, int S, int H, int W, size_t* fwd_ws, size_
     const int gap = std::max(eff_off_, blur_kernel_size(sig) / 2);
     mosaic_ = plan_mosaic(N, H, W, gap);
     const Mosaic& m = mosaic_;
-    DAU_CHECK(plan_gather_tma(m.Nv, S, F_, G_, m.Hv, m.Wv, eff_off_, num_sms_, &fwd_plan_), 4, "no forward gather plan for this shape");
-    DAU_CHECK(plan_gather_tma(m.Nv, F_, S, G_, m.Hv, m.Wv, eff_off_, num_sms_, &bwd_plan_), 4, "no back-propagation gather plan for this shape");
-    DAU_CHECK(plan_grad_tma(m.Nv, S, F_, G_, m.Hv, m.Wv, eff_off_, num_sms_, &grad_plan_), 4, "no gradient plan for this shape");
+    DAU_CHECK(plan_gather_tma(m, S, F_, G_, eff_off_, num_sms_, &fwd_plan_), 4, "no forward gather plan for this shape");
+    DAU_CHECK(plan_gather_tma(m, F_, S, G_, eff_off_, num_sms_, &bwd_plan_), 4, "no back-propagation gather plan for this shape");
+    DAU_CHECK(plan_grad_tma(m, S, F_, G_, eff_off_, num_sms_, &grad_plan_), 4, "no gradient plan for this shape");
     // forward workspace: blurred input | unit table | partial strips of the gather's split tail
     size_t o = 0;
     const size_t blur_in = paired_layout_floats(m.Nv, S, m.Hv, m.Wv);
@@ -140,7 +142,7 @@ void DAUConvLayerB200::Reshape(int N, int S, int H, int W, size_t* fwd_ws, size_
     fwd_ws_ = o;
     // backward workspace: 4 derivative blurs | blurred error | two unit tables | split partials | gather tail strips
     o = 0;
-    const size_t xk_floats = strip_layout_floats(m.Nv, S, m.Hv, m.Wv);
+    const size_t xk_floats = strip_geometry(m, S).total_floats;
     const size_t esg_floats = error_layout_floats(m.Nv, F_, m.Hv, m.Wv);
     off_bwd_xk_ = o;      o = align_up(o + xk_floats * sizeof(float));
     off_bwd_esg_ = o;     o = align_up(o + esg_floats * sizeof(float));
@@ -355,7 +357,7 @@ void DAUConvLayerB200::Backward_gpu(const float* bottom, const float* top_error,
     if (want_params) {
         tic(1, 2, stream);
         if (!want_input) launch_error_relayout(top_error, esg, mosaic_, F_, mrow, mcol, stream, act, crop_);
-        launch_grad_tma(grad_plan_, xk, esg, gtable, partial, mosaic_.Nv, S_, F_, G_, mosaic_.Hv, mosaic_.Wv, stream);
+        launch_grad_tma(grad_plan_, xk, esg, gtable, partial, mosaic_, S_, F_, G_, stream);
         toc(1, 2, stream);
         tic(1, 3, stream);
         GradFinalizeArgs fa;

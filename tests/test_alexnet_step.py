@@ -58,6 +58,7 @@ def test_graph_replay_equals_eager():
     b = _trainer(global_batch=4, device="cuda:0", graph=True)
     for _ in range(6):                    # 3 of b's steps are the capture's warm-up: same count on both
         a.step()
+    b.set_batch()
     b.capture(warmup=3)
     assert b.graph_error is None, b.graph_error
     for _ in range(3):
