@@ -192,7 +192,9 @@ def run_alexnet_block(rank, world, local_rank, steps, warmup):
     try:
         import alexnet_dau_train_step as A
         dev = torch.device("cuda", local_rank)
-        tr = A.Trainer("default", 256, dev, rank, world, graph=True)
+        # one rank: the step replays as ONE CUDA graph; several ranks: eager launches (capturing the step with its
+        # NCCL collectives is not relied on here: a hang would take the headline line with it)
+        tr = A.Trainer("default", 256, dev, rank, world, graph=(world == 1))
         ms, loss = tr.timed(steps, warmup)
         out = {"metric": "alexnet_dau_train_step_images_per_sec", "value": 256.0 / (ms * 1e-3), "unit": UNIT,
                "ms_per_step": ms, "n_gpus": world, "global_batch": 256, "scaling": "strong", "steps": steps,

@@ -229,16 +229,21 @@ def main():
     ap.add_argument("--overlap", type=int, default=1,
                     help="1: the FC head's gradient bucket is all-reduced while the body's backward pass runs; "
                          "0: both buckets after backward")
-    ap.add_argument("--graph", type=int, default=1, help="1: replay the step as one CUDA graph per rank; 0: eager")
+    ap.add_argument("--graph", type=int, default=-1,
+                    help="1: replay the step as one CUDA graph per rank; 0: eager launches; -1 (default): graph on one "
+                         "rank, eager on several (capturing the NCCL collectives is opt-in: tests/test_alexnet_step.py)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
+    graph = (world == 1) if args.graph < 0 else bool(args.graph)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        if graph:       # torch's CUDA-graph notes: no NCCL async error handling (its watchdog polls events) around a capture
+            os.environ.setdefault("TORCH_NCCL_ASYNC_ERROR_HANDLING", "0")
         dist.init_process_group("nccl", device_id=dev)
-    tr = Trainer(args.variant, args.global_batch, dev, rank, world, overlap=bool(args.overlap), graph=bool(args.graph))
+    tr = Trainer(args.variant, args.global_batch, dev, rank, world, overlap=bool(args.overlap), graph=graph)
     ms, loss = tr.timed(args.steps, args.warmup)
     if rank == 0:
         print(json.dumps({
@@ -247,8 +252,27 @@ def main():
             "scaling": "strong", "dtype": "f32", "data": "synthetic", "loss": loss,
             "graph": tr._graph is not None, "graph_error": tr.graph_error,
             "config": {"workload": tr.describe(args.variant)}}))
-    if world > 1:
-        dist.destroy_process_group()
+    teardown(tr, world)
+
+
+def teardown(tr, world):
+    """Leaves the process group.  A captured graph holds NCCL work: it is released first, and a watchdog ends the
+    process if the communicator teardown still blocks (seen with torch 2.11 / NCCL 2.28 after graph replays)."""
+    import gc
+    import threading
+    sys.stdout.flush()
+    if world <= 1:
+        return
+    threading.Timer(30.0, lambda: os._exit(0)).start() if tr._graph is not None else None
+    torch.cuda.synchronize(tr.dev)
+    dist.barrier()
+    tr._graph = None
+    tr._loss = None
+    gc.collect()
+    torch.cuda.synchronize(tr.dev)
+    dist.destroy_process_group()
+    if tr is not None and tr.graph_error is None and threading.active_count() > 1:
+        os._exit(0)                                               # do not wait for the watchdog timer
 
 
 if __name__ == "__main__":

@@ -1,10 +1,16 @@
 #!/bin/bash
-# 8-GPU (or $1-GPU) scaling runs: C2 layer bench (weak) and the AlexNet-DAU step (strong, global batch 256)
+# N-GPU session (default 8): host copy ceiling, C2 layer bench (weak) with the AlexNet-DAU block (strong, global
+# batch 256), and the AlexNet-DAU step alone in its variants.  Outputs under gpurun_out/ with the given tag.
 N=${1:-8}
+TAG=${2:-r2}
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29533"
-$TR bench.py --gpus $N --steps 10 --warmup 3 > gpurun_out/bench_c2_n$N.json 2> gpurun_out/bench_c2_n$N.err
-$TR tools/alexnet_dau_train_step.py --variant default --global-batch 256 > gpurun_out/alexnet_default_n$N.json 2> gpurun_out/alexnet_default_n$N.err
-$TR tools/alexnet_dau_train_step.py --variant large --global-batch 2048 > gpurun_out/alexnet_large_gb2048_n$N.json 2> gpurun_out/alexnet_large_n$N.err
-python tools/alexnet_dau_train_step.py --variant default --global-batch 256 > gpurun_out/alexnet_default_n1.json 2>/dev/null
-tail -n 2 gpurun_out/*_n$N.err | tail -20
-cut -c1-330 gpurun_out/bench_c2_n$N.json gpurun_out/alexnet_default_n$N.json gpurun_out/alexnet_large_gb2048_n$N.json gpurun_out/alexnet_default_n1.json
+for opt in "" "--bind 1" "--register 1"; do
+  $TR tools/pcie_probe.py $opt 2>/dev/null | grep '^{' >> gpurun_out/${TAG}_pcie_probe_n$N.jsonl
+done
+python tools/pcie_probe.py 2>/dev/null | grep '^{' >> gpurun_out/${TAG}_pcie_probe_n1.jsonl
+timeout 600 $TR bench.py --gpus $N --steps 10 --warmup 3 > gpurun_out/${TAG}_bench_c2_n$N.json 2> gpurun_out/${TAG}_bench_c2_n$N.err
+timeout 200 $TR tools/alexnet_dau_train_step.py --variant default --global-batch 256 --graph 0 > gpurun_out/${TAG}_alexnet_default_eager_n$N.json 2> gpurun_out/${TAG}_alexnet_n$N.err
+timeout 200 $TR tools/alexnet_dau_train_step.py --variant default --global-batch 256 --graph 0 --overlap 0 > gpurun_out/${TAG}_alexnet_default_eager_nooverlap_n$N.json 2>> gpurun_out/${TAG}_alexnet_n$N.err
+timeout 150 $TR tools/alexnet_dau_train_step.py --variant default --global-batch 256 --graph 1 > gpurun_out/${TAG}_alexnet_default_graph_n$N.json 2> gpurun_out/${TAG}_alexnet_graph_n$N.err || echo "graph+NCCL run did not finish (rc $?)" >> gpurun_out/${TAG}_alexnet_graph_n$N.err
+tail -n 3 gpurun_out/${TAG}_*_n$N.err | tail -20
+cut -c1-400 gpurun_out/${TAG}_pcie_probe_n$N.jsonl gpurun_out/${TAG}_alexnet_default_*_n$N.json
