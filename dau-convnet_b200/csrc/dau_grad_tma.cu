@@ -62,11 +62,21 @@ namespace {
 
 using namespace tma;
 
-constexpr int R = 4, C = 2, NW = 8, UPW = 12, TW = 64, TH = 4;
-// CTA = 3 warpgroups: warpgroup 0 holds the producer lane and gives its registers away
-// (setmaxnreg.dec), warpgroups 1-2 are the 8 consumer warps and grow to CONS_REGS each
-// (setmaxnreg.inc): every SM sub-partition then holds 1 x PROD_REGS + 2 x CONS_REGS <= 512 per lane.
-constexpr int NTHREADS = (NW + 4) * 32, PROD_REGS = 40, CONS_REGS = 232;
+constexpr int R = 4, C = 2, TW = 64, TH = 4;
+// Two shapes of the CTA, selected by the template parameter UPW = units per warp and pass (= accumulator slots
+// acc[UPW][4] float2 per lane):
+//   UPW 12: 8 consumer warps (2 per SM sub-partition) of 232 registers       -- the shipped shape
+//   UPW  8: 12 consumer warps (3 per sub-partition) of 160 registers          -- more warps to hide latency, fewer
+//           units per pass (Xk re-read from shared memory once per 8 units); measured, see DESIGN.md
+// Warpgroup 0 holds the producer lane and gives its registers away (setmaxnreg.dec); the consumer warpgroups
+// grow to CONS_REGS each (setmaxnreg.inc).
+template <int UPW>
+struct Cfg {
+    static constexpr int NW = UPW == 8 ? 12 : 8;
+    static constexpr int NTHREADS = (NW + 4) * 32;
+    static constexpr int PROD_REGS = UPW == 8 ? 24 : 40;
+    static constexpr int CONS_REGS = UPW == 8 ? 160 : 232;
+};
 constexpr int XK_ROW_BYTES = 32 * C * 2 * 4;            // one (k, r) row of a warp's strip: 512 B
 constexpr int XK_WARP_BYTES = 4 * R * XK_ROW_BYTES;     // 8 KB: [k][r][lane][c][img] of a full strip
 
@@ -111,7 +121,7 @@ __device__ __forceinline__ void item_origin(const TGradParams& p, long long item
 }
 
 // One item of a consumer warp: its Xk strip (RR rows) to registers, then the walk over the units.
-template <int HALO, int RR>
+template <int HALO, int RR, int UPW>
 __device__ __forceinline__ void consume_item(const unsigned char* smem_raw, const TGradParams& p, const GUnit* units,
                                              float2 (&acc)[UPW][4], int warp, int lane, bool s_valid, int kk,
                                              uint64_t* xfull_bar, uint64_t* xempty_bar, uint64_t* full_bar,
@@ -181,14 +191,15 @@ __device__ __forceinline__ void consume_item(const unsigned char* smem_raw, cons
     if (lane == 0) mbar_arrive(&empty_bar[st]);
 }
 
-template <int HALO, int TAIL>
-__global__ void __launch_bounds__(NTHREADS, 1)
+template <int HALO, int TAIL, int UPW>
+__global__ void __launch_bounds__(Cfg<UPW>::NTHREADS, 1)
 dau_grad_tma_kernel(const __grid_constant__ CUtensorMap err_map, const TGradParams p) {
     using GEO = GGeomT<HALO>;
+    constexpr int NW = Cfg<UPW>::NW, PROD_REGS = Cfg<UPW>::PROD_REGS, CONS_REGS = Cfg<UPW>::CONS_REGS;
     extern __shared__ unsigned char smem_dyn[];
     __shared__ uint64_t full_bar[2], empty_bar[2];      // error-tile ring
     __shared__ uint64_t xfull_bar, xempty_bar;           // the single Xk buffer
-    __shared__ GUnit s_units[NW][UPW];
+    __shared__ GUnit s_units[NW][UPW];               // (UPW: template parameter)
     unsigned char* smem_raw = smem_dyn + ((128u - (smem_u32(smem_dyn) & 127u)) & 127u);
 
     const int tid = threadIdx.x, lane = tid & 31;
@@ -213,23 +224,7 @@ dau_grad_tma_kernel(const __grid_constant__ CUtensorMap err_map, const TGradPara
         mbar_init(&xfull_bar, 1); mbar_init(&xempty_bar, NW);
         fence_barrier_init();
     }
-    if (warp >= 0 && lane < UPW) {
-        // slots beyond the chunk's units are dummies (zero weights, in-tile offsets): the unit loop
-        // is branch-free so that one unit's prologue overlaps the previous unit's math
-        GUnit gu;
-        gu.w00 = gu.w01 = gu.w10 = gu.w11 = make_float2(0.f, 0.f);
-        gu.offx = GEO::HX; gu.offy = GEO::HY; gu.tile_off = 0; gu.pad = 0;
-        if (s0 + warp < p.S && lane < nunits) {
-            const int fi = lane / ngc, gi = lane - fi * ngc;
-            const UnitRec r = p.table[((size_t)(s0 + warp) * F + f0 + fi) * G + g0 + gi];
-            gu.w00 = make_float2(r.w00, r.w00); gu.w01 = make_float2(r.w01, r.w01);
-            gu.w10 = make_float2(r.w10, r.w10); gu.w11 = make_float2(r.w11, r.w11);
-            gu.offx = r.offx_h; gu.offy = r.offy_h;
-            gu.tile_off = fi * (p.feat_bytes_al / 8);  // float2 offset of the feature's error tile
-        }
-        s_units[warp][lane] = gu;
-    }
-    __syncthreads();
+    __syncthreads();                                   // barriers initialised: the producer starts copying NOW
 
     if (warp < 0) {
         asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;\n" ::"n"(PROD_REGS));
@@ -263,8 +258,27 @@ dau_grad_tma_kernel(const __grid_constant__ CUtensorMap err_map, const TGradPara
         return;
     }
 
-    // ---- consumer warps: warp = input channel s0 + warp -------------------------------------------
+    // ---- consumer warps: the unit records of this CTA, fetched while the first copies are in flight ----
     asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;\n" ::"n"(CONS_REGS));
+    if (lane < UPW) {
+        // slots beyond the chunk's units are dummies (zero weights, in-tile offsets): the unit loop
+        // is branch-free so that one unit's prologue overlaps the previous unit's math
+        GUnit gu;
+        gu.w00 = gu.w01 = gu.w10 = gu.w11 = make_float2(0.f, 0.f);
+        gu.offx = GEO::HX; gu.offy = GEO::HY; gu.tile_off = 0; gu.pad = 0;
+        if (s0 + warp < p.S && lane < nunits) {
+            const int fi = lane / ngc, gi = lane - fi * ngc;
+            const UnitRec r = p.table[((size_t)(s0 + warp) * F + f0 + fi) * G + g0 + gi];
+            gu.w00 = make_float2(r.w00, r.w00); gu.w01 = make_float2(r.w01, r.w01);
+            gu.w10 = make_float2(r.w10, r.w10); gu.w11 = make_float2(r.w11, r.w11);
+            gu.offx = r.offx_h; gu.offy = r.offy_h;
+            gu.tile_off = fi * (p.feat_bytes_al / 8);  // float2 offset of the feature's error tile
+        }
+        s_units[warp][lane] = gu;                      // a warp reads only its own row: a warp-level sync is enough
+    }
+    __syncwarp();
+
+    // warp = input channel s0 + warp
     const bool s_valid = warp < nsv;
     float2 acc[UPW][4];                                // {image 0, image 1} partial sums
 #pragma unroll
@@ -273,11 +287,11 @@ dau_grad_tma_kernel(const __grid_constant__ CUtensorMap err_map, const TGradPara
         for (int k = 0; k < 4; ++k) acc[u][k] = make_float2(0.f, 0.f);
 
     for (int kk = 0; kk < nfull; ++kk)
-        consume_item<HALO, R>(smem_raw, p, s_units[warp], acc, warp, lane, s_valid, kk, &xfull_bar, &xempty_bar,
+        consume_item<HALO, R, UPW>(smem_raw, p, s_units[warp], acc, warp, lane, s_valid, kk, &xfull_bar, &xempty_bar,
                               full_bar, empty_bar);
     if (TAIL > 0) {
         for (int kk = nfull; kk < nsteps; ++kk)
-            consume_item<HALO, (TAIL > 0 ? TAIL : 1)>(smem_raw, p, s_units[warp], acc, warp, lane, s_valid, kk,
+            consume_item<HALO, (TAIL > 0 ? TAIL : 1), UPW>(smem_raw, p, s_units[warp], acc, warp, lane, s_valid, kk,
                                                       &xfull_bar, &xempty_bar, full_bar, empty_bar);
     }
 
@@ -304,26 +318,35 @@ dau_grad_tma_kernel(const __grid_constant__ CUtensorMap err_map, const TGradPara
 
 constexpr int kHalos[4] = {4, 8, 16, 32};
 
-template <int HALO, int TAIL>
+template <int HALO, int TAIL, int UPW>
 void launch_t(const GradPlan& plan, const CUtensorMap& map, const TGradParams& p, cudaStream_t stream) {
     static PerDeviceOnce once;                 // the attribute is per (kernel, device)
     if (once.need()) {
-        DAU_CUDA_CHECK(cudaFuncSetAttribute(dau_grad_tma_kernel<HALO, TAIL>,
-                                            cudaFuncAttributeMaxDynamicSharedMemorySize, 221 * 1024));
+        DAU_CUDA_CHECK(cudaFuncSetAttribute(dau_grad_tma_kernel<HALO, TAIL, UPW>,
+                                            cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));   // + up to 6.2 KB static <= 227 KB
         once.done();
     }
     dim3 grid(plan.grid_x, plan.grid_y, plan.grid_z);
-    dau_grad_tma_kernel<HALO, TAIL><<<grid, NTHREADS, plan.smem_bytes, stream>>>(map, p);
+    dau_grad_tma_kernel<HALO, TAIL, UPW><<<grid, Cfg<UPW>::NTHREADS, plan.smem_bytes, stream>>>(map, p);
+}
+
+template <int HALO, int UPW>
+void launch_u(const GradPlan& plan, const CUtensorMap& map, const TGradParams& p, cudaStream_t stream) {
+    switch (plan.tail) {
+        case 0: launch_t<HALO, 0, UPW>(plan, map, p, stream); break;
+        case 1: launch_t<HALO, 1, UPW>(plan, map, p, stream); break;
+        case 2: launch_t<HALO, 2, UPW>(plan, map, p, stream); break;
+        default: launch_t<HALO, 3, UPW>(plan, map, p, stream); break;
+    }
 }
 
 template <int HALO>
 void launch_h(const GradPlan& plan, const CUtensorMap& map, const TGradParams& p, cudaStream_t stream) {
-    switch (plan.tail) {
-        case 0: launch_t<HALO, 0>(plan, map, p, stream); break;
-        case 1: launch_t<HALO, 1>(plan, map, p, stream); break;
-        case 2: launch_t<HALO, 2>(plan, map, p, stream); break;
-        default: launch_t<HALO, 3>(plan, map, p, stream); break;
-    }
+#ifdef DAU_DEV_SWITCHES
+    if (plan.upw == 8) { launch_u<HALO, 8>(plan, map, p, stream); return; }
+    if (plan.upw == 16) { launch_u<HALO, 16>(plan, map, p, stream); return; }
+#endif
+    launch_u<HALO, 12>(plan, map, p, stream);
 }
 
 template <int HALO>
@@ -367,7 +390,16 @@ bool plan_grad_tma(const Mosaic& m, int S, int F, int G, int max_off, int num_sm
         case 2: fill_t<16>(pl); break;
         default: fill_t<32>(pl); break;
     }
+    // Units per warp and pass: 12 (8 consumer warps of 232 registers).  Measured alternatives, both slower and
+    // therefore only in development builds: 16 (same warps, 128 accumulator registers: C2
+    // 12.21 -> 12.81 ms, L4 6.05 -> 6.50 ms) and 8 (12 consumer warps of 160 registers).
+    int UPW = 12;
+#ifdef DAU_DEV_SWITCHES
+    if (getenv("DAU_GRAD_UPW")) { const int u = atoi(getenv("DAU_GRAD_UPW")); UPW = (u == 16 || u == 8) ? u : 12; }
+#endif
+    const int NW = UPW == 8 ? 12 : 8;
     const size_t budget = 220 * 1024 - 128, xk_bytes = (size_t)NW * XK_WARP_BYTES;
+    pl.upw = UPW;
     pl.g_chunk = G < UPW ? G : UPW;
     int fc = UPW / pl.g_chunk;
     if (fc > F) fc = F;

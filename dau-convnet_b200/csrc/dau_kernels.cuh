@@ -123,6 +123,7 @@ struct GradPlan {
     int g_chunk;               // units of one (s,f) handled per pass (G or 16)
     int n_splits;              // CTAs along the (image,tile) reduction axis
     int tail;                  // rows of the tail strips (H % 4): selects the kernel instantiation
+    int upw;                   // accumulator slots per warp (12 or 16): selects the kernel instantiation
     size_t smem_bytes;
     int grid_x, grid_y, grid_z;
     size_t partial_floats;     // n_splits * 4 * S*G*F

@@ -13,9 +13,10 @@ on libdau_conv_b200.so through dau_conv.DAUConv2d; everything else is stock torc
 
 One step = forward, loss, backward, all-reduce of ALL gradients, SGD(momentum) update, on synthetic
 data.  How the step is laid out (`Trainer`):
-  * parameters, gradients and momentum live in two flat buffers each -- "head" (the three FC layers,
-    235 MB, 95 % of the bytes) and "body" (conv1 + the DAU layers) -- so a bucket is ONE all-reduce and
-    the optimizer is two element-wise kernels per bucket instead of three per parameter;
+  * the parameters form two buckets -- "head" (the three FC layers, 235 MB, 95 % of the bytes) and "body"
+    (conv1 + the DAU layers); a bucket's gradients travel in ONE coalesced NCCL all-reduce; gradients are
+    dropped (not zero-filled) before every step so autograd assigns instead of accumulating, and the
+    optimizer is one fused multi-tensor SGD kernel: no extra pass over the 235 MB of FC gradients;
   * the loss is sum_i CE_i / global_batch, so per-rank gradients ADD to the single-GPU gradient: the
     all-reduce is a plain SUM, uneven shards are exact, nothing is divided afterwards;
   * backward runs in two pieces: through the FC head first, whose bucket is all-reduced (NCCL, async,
@@ -62,25 +63,32 @@ class AlexNetDAU(nn.Module):
 
 
 class _Bucket(object):
-    """Parameters, gradients and momentum of a group of parameters as three flat fp32 buffers; the
-    parameters' .data and .grad are views into them."""
+    """A group of parameters whose gradients travel in ONE (coalesced) all-reduce.  The parameters live in one flat
+    buffer (views); gradients are whatever tensors autograd ASSIGNS during backward (they are dropped, not
+    zero-filled, before every step, so there is no fill pass and no accumulate pass over the 235 MB of FC weights)."""
 
     def __init__(self, params, device):
         self.params = [p for p in params if p.requires_grad]
         n = sum(p.numel() for p in self.params)
-        self.p = torch.empty(n, device=device); self.g = torch.zeros(n, device=device)
-        self.m = torch.zeros(n, device=device)
+        self.p = torch.empty(n, device=device)
         o = 0
         for p in self.params:
             k = p.numel()
             self.p[o:o + k].copy_(p.data.reshape(-1))
             p.data = self.p[o:o + k].view_as(p)
-            p.grad = self.g[o:o + k].view_as(p)
             o += k
 
-    def sgd(self, lr, momentum):
-        self.m.mul_(momentum).add_(self.g)
-        self.p.add_(self.m, alpha=-lr)
+    def drop_grads(self):
+        for p in self.params:
+            p.grad = None
+
+    def grads(self):
+        return [p.grad for p in self.params]
+
+    @property
+    def g(self):
+        """Flat copy of the gradients (tests)."""
+        return torch.cat([p.grad.reshape(-1) for p in self.params])
 
 
 class Trainer(object):
@@ -93,6 +101,8 @@ class Trainer(object):
         self.model = AlexNetDAU(VARIANTS[variant], num_classes).to(self.dev)
         self.head = _Bucket(self.model.classifier.parameters(), self.dev)
         self.body = _Bucket(self.model.features.parameters(), self.dev)
+        # one fused multi-tensor kernel per step: momentum and update in a single pass over p, g and m
+        self.opt = torch.optim.SGD(self.head.params + self.body.params, lr=lr, momentum=momentum, fused=True)
         # images [lo, hi) of the global batch (dau_conv.distributed.shard_range: uneven shards allowed)
         from dau_conv.distributed import shard_range
         self.lo, self.hi = shard_range(self.global_batch, rank, world)
@@ -122,15 +132,19 @@ class Trainer(object):
 
     # -- one step -----------------------------------------------------------------------------------------
     def _reduce(self, bucket):
+        """SUM all-reduce of the bucket's gradient tensors as ONE coalesced NCCL launch, asynchronous."""
         if self.world > 1 and dist.is_available() and dist.is_initialized():
-            return dist.all_reduce(bucket.g, op=dist.ReduceOp.SUM, async_op=True)
+            with dist._coalescing_manager(device=self.dev, async_ops=True) as cm:
+                for g in bucket.grads():
+                    dist.all_reduce(g, op=dist.ReduceOp.SUM)
+            return cm
         return None                                               # one rank (or shards simulated on one GPU by a test)
 
     def compute_gradients(self):
         """Forward + backward of this rank's shard; leaves the SUMMED (all-reduced) gradients of the global
         batch in the flat buffers and returns the shard's part of the loss."""
         m = self.model
-        self.head.g.zero_(); self.body.g.zero_()
+        self.head.drop_grads(); self.body.drop_grads()
         f = m.features(self.x)
         fd = f.detach().requires_grad_(True)
         loss = nn.functional.cross_entropy(m.classifier(fd), self.target, reduction="sum") / self.global_batch
@@ -147,7 +161,7 @@ class Trainer(object):
 
     def _eager_step(self):
         loss = self.compute_gradients()
-        self.head.sgd(self.lr, self.momentum); self.body.sgd(self.lr, self.momentum)
+        self.opt.step()
         return loss
 
     def capture(self, warmup=3):
