@@ -41,6 +41,8 @@ CONFIGS = {
     "c1": (16, 32, 32, (1, 2), 32, 32, 9, 3.0),
     "c2": (128, 128, 128, (2, 2), 64, 64, 9, 4.0),
     "c4": (256, 512, 512, (1, 2), 28, 28, 17, 8.0),
+    # the reference's own speed test (plugins/tensorflow/tests/dau_conv_test.py:504-516): a latency-bound layer
+    "st": (32, 128, 32, (2, 1), 16, 16, 9, 3.0),
     # AlexNet-DAU default DAU layers (assumption A1 in BASELINE.md), per-GPU batch 256
     "l2": (256, 96, 256, (1, 2), 27, 27, 9, 3.0),
     "l3": (256, 256, 384, (1, 2), 13, 13, 9, 3.0),
@@ -352,6 +354,27 @@ def run_ours(args, rank, world, local_rank):
                 "peak_gbs": hbm_peak, "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)"},
     }
 
+    # ---- the same step replayed as ONE CUDA graph (launch-latency-bound layers; the headline stays eager) ---
+    graph_block = None
+    if world == 1:
+        try:
+            gs = dau_conv.GraphedStep(h, x, e, w, mu1, mu2, sigma)
+            for _ in range(3):
+                gs.replay()
+            torch.cuda.synchronize(dev)
+            reps = max(args.steps, 10)
+            ev0.record()
+            for _ in range(reps):
+                gs.replay()
+            ev1.record()
+            torch.cuda.synchronize(dev)
+            g_ms = ev0.elapsed_time(ev1) / reps
+            graph_block = {"ms_per_step": g_ms, "value": N / (g_ms * 1e-3), "unit": UNIT, "steps": reps,
+                           "what": "dau_forward + dau_backward captured once by dau_conv.GraphedStep and replayed"}
+            del gs
+        except Exception as ex:
+            graph_block = {"error": "%s: %s" % (type(ex).__name__, str(ex)[:200])}
+
     # ---- end to end: host buffers in, host buffers out, through the same public API ------------
     e2e_steps = max(1, min(args.steps, 5))
     xp, ep = torch.from_numpy(xh).pin_memory(), torch.from_numpy(eh).pin_memory()
@@ -405,6 +428,7 @@ def run_ours(args, rank, world, local_rank):
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": config_block(args.config, world),
         "roofline": roofline, "cpu_baseline": cpu_baseline, "alexnet_dau": alexnet, "reference_cuda": reference_cuda,
+        "cuda_graph": graph_block,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "steps": e2e_steps, "max_chunk_images": e2e_chunk,
                 "what": "dau_train_step_host: pinned host x, top_error -> device; fwd+bwd; y, dL/dx and the "

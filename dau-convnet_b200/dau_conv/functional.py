@@ -199,6 +199,48 @@ class DAULayerHandle(object):
         return grads
 
 
+class GraphedStep(object):
+    """forward + backward of one handle captured ONCE in a CUDA graph and replayed: for layers whose whole
+    step is shorter than the launch latency of its dozen kernels (the reference's own speed-test shape,
+    plugins/tensorflow/tests/dau_conv_test.py:504-628, or BASELINE config C1).  Every call of the C ABI is
+    stream-ordered and allocation-free once sigma is known (set_sigma_hint), so the capture is plain stream
+    capture; the graph is keyed on the tensors it was captured with -- write new data INTO them.
+    Parameter gradients are zeroed inside the graph (the op's contract: it accumulates into pre-zeroed buffers)."""
+
+    def __init__(self, handle, x, top_error, w, mu1, mu2, sigma, flags=_lib.GRAD_ALL):
+        self.h = handle
+        self.x, self.e, self.w, self.mu1, self.mu2, self.sigma = x, top_error, w, mu1, mu2, sigma
+        N, S, H, W = x.shape
+        handle.reshape(N, S, H, W)
+        self.y = torch.empty((N, handle.settings.num_output) + handle.out_hw, dtype=torch.float32, device=x.device)
+        self.flat = torch.zeros((4,) + tuple(w.shape), dtype=torch.float32, device=x.device)
+        self.grads = [self.flat[k] for k in range(4)]
+        self.flags = flags
+        handle.workspace(max(handle.fwd_bytes, handle.bwd_bytes))
+        side = torch.cuda.Stream(x.device)
+        side.wait_stream(torch.cuda.current_stream(x.device))
+        with torch.cuda.stream(side):                    # warm-up outside the capture (lazy attribute / table setup)
+            for _ in range(2):
+                self._eager()
+        torch.cuda.current_stream(x.device).wait_stream(side)
+        torch.cuda.synchronize(x.device)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self._eager()
+
+    def _eager(self):
+        self.h.forward(self.x, self.w, self.mu1, self.mu2, self.sigma, out=self.y)
+        self.flat.zero_()
+        out = self.h.backward(self.x, self.e, self.w, self.mu1, self.mu2, self.sigma, flags=self.flags, grads=self.grads)
+        self.dx = out[0]
+        return out
+
+    def replay(self):
+        """Runs the captured step; returns (y, dx, dw, dmu1, dmu2, dsigma) -- the SAME tensors every time."""
+        self.graph.replay()
+        return (self.y, self.dx) + tuple(self.grads)
+
+
 _HANDLES = {}
 
 

@@ -513,3 +513,30 @@ def test_offset_hint_selects_the_displacement_bucket():
         return np.clip(m, -4.0, 4.0).astype(np.float32)
     close(y.cpu().numpy(), O.forward(x, w, clamp(big1), clamp(big2), [0.5]), "y with clamped offsets")
     h.set_offset_hint(None)
+
+
+def test_graphed_step_replays_the_eager_step_bit_for_bit():
+    """dau_conv.GraphedStep: forward + backward captured once in a CUDA graph (latency-bound layers, the
+    reference's speed-test shape dau_conv_test.py:504-516).  Replays read the CURRENT contents of the captured
+    tensors: new data written into them gives the new result, identical to the eager calls."""
+    import torch
+    import dau_conv
+    shape = (4, 16, 16, 8, 6, (2, 1), 9, 3)
+    dev = torch.device("cuda:0")
+    a = dict(num_output=6, number_units_x=2, number_units_y=1, kernel_size=9, pad=4)
+    h = dau_conv.get_handle(dev, **a)
+    h.set_sigma_hint(0.5)
+    x, err, w, mu1, mu2, ks = _case(shape, 17)
+    sig = np.full(w.shape, 0.5, np.float32)
+    t = [torch.from_numpy(v).to(dev) for v in (x, err, w, mu1, mu2, sig)]
+    gs = dau_conv.GraphedStep(h, *t)
+    for seed in (17, 18):
+        x2, err2, _, _, _, _ = _case(shape, seed)
+        t[0].copy_(torch.from_numpy(x2)); t[1].copy_(torch.from_numpy(err2))
+        got = [v.clone() for v in gs.replay()]
+        y = h.forward(t[0], t[2], t[3], t[4], t[5])
+        ref = (y,) + tuple(h.backward(t[0], t[1], t[2], t[3], t[4], t[5]))
+        torch.cuda.synchronize()
+        for g_, r_ in zip(got, ref):
+            assert torch.equal(g_, r_)
+    close(got[0].cpu().numpy(), O.forward(x2, w, mu1, mu2, [0.5]), "y graphed")
