@@ -257,6 +257,15 @@ int dau_mosaic_to_real(const int* q, int N, int nv, int vy, int vx, int* n, int*
     return dau::mosaic_to_real(m, nv, vy, vx, n, y, x) ? 1 : 0;
 }
 
+dau_status_t dau_bias_grad_static(int device, const float* top_error, const float* top_data, float* dbias,
+                                  int N, int F, int H_out, int W_out, void* stream) {
+    return guarded([&] {
+        dau::DeviceGuard guard(device);                 // negative: the caller's current device
+        DAU_CHECK(H_out > 0 && W_out > 0, 1, "dau_bias_grad_static: N, F, H_out and W_out must be positive");
+        dau::launch_bias_grad_static(top_error, top_data, dbias, N, F, H_out * W_out, (cudaStream_t)stream);
+    });
+}
+
 int dau_edge_mask_rule(int extent) { return DAUConvLayerB200::edge_mask_rule(extent) ? 1 : 0; }
 
 dau_status_t dau_debug_unit_tables(dau_handle_t* h, const float* w, const float* mu1, const float* mu2,

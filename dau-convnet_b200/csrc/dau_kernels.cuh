@@ -172,6 +172,12 @@ size_t bias_grad_partial_floats(int F);
 void launch_bias_grad(const float* err, const float* act, float* dbias, float* partial, int N, int F, int HW,
                       cudaStream_t stream);
 
+// the same with the partials in a static device array of this library (no workspace, nothing allocated);
+// F <= static_bias_grad_max_features(); the CURRENT device is used; calls that overlap on one GPU race
+int static_bias_grad_max_features();
+void launch_bias_grad_static(const float* err, const float* act, float* dbias, int N, int F, int HW,
+                             cudaStream_t stream);
+
 // FP32 FMA peak probe (register-resident FFMA chains on every SM)
 void launch_fma_probe(float* sink, int iters, int blocks, cudaStream_t stream);
 

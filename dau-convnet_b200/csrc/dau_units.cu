@@ -9,6 +9,8 @@
 // "negate mu for back-propagation" memcpy + cublasSscal (base_dau_conv_layer.cu:299-315).
 #include "dau_kernels.cuh"
 
+#include <mutex>
+
 namespace dau {
 
 namespace {
@@ -179,6 +181,47 @@ void launch_bias_grad(const float* err, const float* act, float* dbias, float* p
     const int slices = N < kBiasSlices ? N : kBiasSlices;
     bias_grad_kernel<<<dim3(F, slices), 256, 0, stream>>>(err, act, partial, N, F, HW);
     bias_finalize_kernel<<<(F + 127) / 128, 128, 0, stream>>>(partial, dbias, F, slices);
+    DAU_CUDA_CHECK(cudaGetLastError());
+}
+
+// ---- allocation-free bias gradient (dau_bias_grad_static) ----------------------------------------------
+// The same two kernels as launch_bias_grad, with the per-slice partials in a file-scope device array instead of
+// the caller's workspace, for callers that may not allocate (code under CUDA graph capture, serving loops).
+// 16 slices x 4096 features x 4 B = 256 KB, held by every GPU that loads this library until the process exits.
+// In host code the array's NAME is a host-side stand-in, not a device address: the address comes from
+// cudaGetSymbolAddress, once per device, with that device current.
+constexpr int kStaticBiasMaxF = 4096;
+static __device__ __align__(256) float g_static_bias_partials[kBiasSlices * kStaticBiasMaxF];
+
+int static_bias_grad_max_features() { return kStaticBiasMaxF; }
+
+void launch_bias_grad_static(const float* err, const float* act, float* dbias, int N, int F, int HW,
+                             cudaStream_t stream) {
+    DAU_CHECK(err != nullptr && dbias != nullptr, 1, "dau_bias_grad_static: NULL tensor pointer");
+    DAU_CHECK(N > 0 && F > 0 && HW > 0, 1, "dau_bias_grad_static: N, F, H_out and W_out must be positive");
+    DAU_CHECK(F <= kStaticBiasMaxF, 4,
+              "dau_bias_grad_static: F = " + std::to_string(F) + " exceeds the static scratch limit of " +
+              std::to_string(kStaticBiasMaxF) + " features (use dau_backward with DAU_GRAD_BIAS and a workspace)");
+    static std::mutex mu;
+    static float* scratch_of_device[256] = {};
+    int dev = -1;
+    DAU_CUDA_CHECK(cudaGetDevice(&dev));
+    DAU_CHECK(dev >= 0 && dev < 256, 4, "dau_bias_grad_static: device ordinal out of range");
+    float* scratch = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        scratch = scratch_of_device[dev];
+        if (scratch == nullptr) {                      // set-up, once per device, that device being current
+            DAU_CUDA_CHECK(cudaGetSymbolAddress((void**)&scratch, g_static_bias_partials));
+            DAU_CHECK(scratch != nullptr, 2, "dau_bias_grad_static: cudaGetSymbolAddress returned NULL");
+            scratch_of_device[dev] = scratch;
+        }
+    }
+    // nothing in the array has to start at zero: stage 1 writes partial[slice][f] for every (slice < slices, f < F)
+    // and stage 2 reads exactly those entries, so whatever an earlier call left behind is never read
+    const int slices = N < kBiasSlices ? N : kBiasSlices;
+    bias_grad_kernel<<<dim3(F, slices), 256, 0, stream>>>(err, act, scratch, N, F, HW);
+    bias_finalize_kernel<<<(F + 127) / 128, 128, 0, stream>>>(scratch, dbias, F, slices);
     DAU_CUDA_CHECK(cudaGetLastError());
 }
 

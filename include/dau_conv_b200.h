@@ -195,6 +195,24 @@ dau_status_t dau_train_step_host(dau_handle_t* h, int N, int S, int H, int W, in
 dau_status_t dau_plan_mosaic(int N, int H, int W, int gap, int* out10);
 int dau_mosaic_to_real(const int* mosaic10, int N, int nv, int vy, int vx, int* n, int* y, int* x);
 
+/* Allocation-free bias gradient.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  dbias[f] += sum_{n,y,x} top_error[n,f,y,x], and with top_data != NULL only where
+ * top_data[n,f,y,x] > 0 (the fused ReLU backward) -- exactly what dau_backward / dau_backward_act compute for
+ * DAU_GRAD_BIAS (same two kernels, same summation order, same bits), but the per-slice partial sums live in a
+ * file-scope `static __device__` array of libdau_conv_b200.so instead of the caller's workspace:
+ *   - limit: F <= 4096 (DAU_STATIC_BIAS_MAX_F); a larger F is refused with DAU_ERR_UNSUPPORTED and a message;
+ *   - cost: 16 x 4096 x 4 B = 256 KB of device memory on every GPU that loads the library, until the process exits;
+ *   - the call allocates and frees nothing (no cudaMalloc / cudaFree, no allocating library routine); its first
+ *     call on a device looks the array's address up once (cudaGetSymbolAddress) -- make that call outside a capture;
+ *   - every call on a GPU shares the one array: calls that OVERLAP on the same GPU (two streams, two threads) race;
+ *     stream-ordered calls are safe.  Nothing in the array has to start at zero: a call writes every entry it reads.
+ * device: CUDA ordinal, negative = the calling thread's current device (left as found).  All pointers are DEVICE
+ * memory owned by the caller; dbias[F] is accumulated into.  No handle, no workspace. */
+#define DAU_STATIC_BIAS_MAX_F 4096
+dau_status_t dau_bias_grad_static(int device, const float* top_error_dev, const float* top_data_dev,
+                                  float* dbias_dev, int N, int F, int H_out, int W_out, void* stream);
+
 /* ignore_edge_gradients rule for one output extent: 1 if the last row / column of the top error is
  * zeroed (extent a multiple of the reference's patch size 64 / 32 / 16 / 8, the largest that is
  * <= extent; plugins/tensorflow/tests/dau_conv_test.py:110-136, base_dau_conv_layer.cpp:763-771). */
