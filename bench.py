@@ -187,21 +187,43 @@ def run_reference(args, rank, world):
     }))
 
 
-def run_alexnet_block(rank, world, local_rank, steps, warmup):
-    """AlexNet-DAU-default training step at GLOBAL batch 256 (BASELINE.json configs[2]): strong scaling."""
+def run_alexnet_block(rank, world, local_rank, steps, warmup, on_hang=None):
+    """AlexNet-DAU-default training step at GLOBAL batch 256 (BASELINE.json configs[2]): strong scaling.
+    The step is measured with eager launches first and then replayed as ONE CUDA graph per rank (at N > 1 with both
+    NCCL all-reduces captured inside); the block's `value` is the graphed step when that ran, the eager one otherwise,
+    and both times are reported.  A capture with collectives inside that does not come back within GRAPH_BUDGET_S
+    calls on_hang(eager block), which prints the headline line with the eager numbers and ends the process."""
+    GRAPH_BUDGET_S = 120.0
     sys.path.insert(0, os.path.join(ROOT, "tools"))
     import torch
     try:
         import alexnet_dau_train_step as A
         dev = torch.device("cuda", local_rank)
-        # one rank: the step replays as ONE CUDA graph; several ranks: eager launches (capturing the step with its
-        # NCCL collectives is not relied on here: a hang would take the headline line with it)
-        tr = A.Trainer("default", 256, dev, rank, world, graph=(world == 1))
+        tr = A.Trainer("default", 256, dev, rank, world, graph=False)
         ms, loss = tr.timed(steps, warmup)
         out = {"metric": "alexnet_dau_train_step_images_per_sec", "value": 256.0 / (ms * 1e-3), "unit": UNIT,
                "ms_per_step": ms, "n_gpus": world, "global_batch": 256, "scaling": "strong", "steps": steps,
-               "warmup": warmup, "loss": loss, "cuda_graph": tr._graph is not None, "graph_error": tr.graph_error,
-               "workload": tr.describe("default")}
+               "warmup": warmup, "loss": loss, "cuda_graph": False, "graph_error": None,
+               "ms_per_step_eager": ms, "ms_per_step_graph": None, "workload": tr.describe("default")}
+        timer = None
+        if world > 1 and on_hang is not None:
+            timer = threading.Timer(GRAPH_BUDGET_S, on_hang, args=(dict(out, graph_error="capture / replay with NCCL "
+                                                                        "inside did not finish in %d s" % GRAPH_BUDGET_S),))
+            timer.daemon = True
+            timer.start()
+        tr._want_graph = True
+        tr.capture()
+        if tr._graph is not None:
+            ms_g, loss_g = tr.timed(steps, 2)
+            out.update({"value": 256.0 / (ms_g * 1e-3), "ms_per_step": ms_g, "ms_per_step_graph": ms_g, "loss": loss_g,
+                        "cuda_graph": True, "workload": tr.describe("default")})
+        else:
+            out["graph_error"] = tr.graph_error
+        tr.sync()
+        if timer is not None:
+            timer.cancel()
+        tr._graph = None
+        tr._loss = None
         del tr
         torch.cuda.empty_cache()
         return out
@@ -407,9 +429,31 @@ def run_ours(args, rank, world, local_rank):
     d2h = yp.numel() * 4 + dxp.numel() * 4 + gp.numel() * 4
 
     # ---- secondary blocks (after, and outside, every timed region of the headline metric) -----------------
+    def line(alexnet, reference_cuda=None, cpu_baseline=None):
+        return json.dumps({
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": config_block(args.config, world),
+            "roofline": roofline, "cpu_baseline": cpu_baseline, "alexnet_dau": alexnet, "reference_cuda": reference_cuda,
+            "cuda_graph": graph_block,
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "steps": e2e_steps, "max_chunk_images": e2e_chunk,
+                    "what": "dau_train_step_host: pinned host x, top_error -> device; fwd+bwd; y, dL/dx and the "
+                            "4 parameter gradients -> pinned host; copies overlapped with the kernels chunk by chunk"},
+            "gpu_launches": launches, "clocks": clk if sampler else None,
+        })
+
+    def on_hang(alexnet_eager):
+        # the graphed AlexNet step (NCCL inside) did not come back: the line goes out with the eager numbers
+        if rank == 0:
+            print(line(alexnet_eager))
+            sys.stdout.flush()
+        os._exit(0)
+
     alexnet = None
     if args.config == "c2" and not args.no_alexnet:
-        alexnet = run_alexnet_block(rank, world, local_rank, args.alexnet_steps, 3)
+        alexnet = run_alexnet_block(rank, world, local_rank, args.alexnet_steps, 3, on_hang)
     if rank != 0:
         return
     reference_cuda = None
@@ -422,19 +466,8 @@ def run_ours(args, rank, world, local_rank):
         cpu_baseline = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                         "sample": "%d of the %d images of the batch, one fwd+bwd pass (%.1f s); oracle/dau_cpu.c, "
                                   "C/OpenMP restatement of the reference CPU path" % (n_cpu, N, ms / 1e3)}
-    print(json.dumps({
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": config_block(args.config, world),
-        "roofline": roofline, "cpu_baseline": cpu_baseline, "alexnet_dau": alexnet, "reference_cuda": reference_cuda,
-        "cuda_graph": graph_block,
-        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "steps": e2e_steps, "max_chunk_images": e2e_chunk,
-                "what": "dau_train_step_host: pinned host x, top_error -> device; fwd+bwd; y, dL/dx and the "
-                        "4 parameter gradients -> pinned host; copies overlapped with the kernels chunk by chunk"},
-        "gpu_launches": launches, "clocks": clk if sampler else None,
-    }))
+    print(line(alexnet, reference_cuda, cpu_baseline))
+    sys.stdout.flush()
 
 
 def main():
@@ -465,6 +498,9 @@ def main():
         import torch
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        # the AlexNet block captures NCCL collectives in a CUDA graph: torch's notes ask for the NCCL watchdog's
+        # asynchronous error handling to be off around captures (it polls CUDA events)
+        os.environ.setdefault("TORCH_NCCL_ASYNC_ERROR_HANDLING", "0")
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     try:
@@ -472,7 +508,13 @@ def main():
     finally:
         if world > 1:
             import torch.distributed as dist
+            sys.stdout.flush()
+            # a communicator that replayed captured work has been seen to block in its teardown: bounded
+            guard = threading.Timer(30.0, lambda: os._exit(0))
+            guard.daemon = True
+            guard.start()
             dist.destroy_process_group()
+            guard.cancel()
 
 
 if __name__ == "__main__":

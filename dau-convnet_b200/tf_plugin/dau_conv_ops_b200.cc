@@ -105,7 +105,9 @@ class DAUOpBase : public OpKernel {
     ~DAUOpBase() override { if (h_) dau_destroy(h_); }
 
  protected:
-    // Validates the five tensors (dau_conv_op.cpp:150-208) and (re)plans the handle for this shape.
+    // Validates the five tensors (dau_conv_op.cpp:150-208) and (re)plans the handle for this shape.  The caller
+    // holds mu_ from here until its launch and NaN read are enqueued: two concurrent Compute() calls on one kernel
+    // instance with different shapes must not re-plan the shared handle under a running call.
     Status Prepare(OpKernelContext* ctx, const Tensor& input, const Tensor& w, const Tensor& mu1, const Tensor& mu2,
                    const Tensor& sigma, size_t* fwd, size_t* bwd) {
         if (input.dims() != 4) return errors::InvalidArgument("DAUConv: input must be [N, C, H, W]");
@@ -114,7 +116,6 @@ class DAUOpBase : public OpKernel {
                 p->dim_size(2) != st_.number_units_x * st_.number_units_y || p->dim_size(3) != st_.num_output)
                 return errors::InvalidArgument("DAUConv: parameters must be [1, S, G, F]");
         }
-        std::lock_guard<std::mutex> lock(mu_);
         if (!h_ && dau_create(&st_, /*device=*/-1, &h_) != DAU_OK) return errors::Internal(dau_last_error());
         std::vector<int64_t> shape{input.dim_size(0), input.dim_size(1), input.dim_size(2), input.dim_size(3)};
         if (shape != shape_) {
@@ -149,6 +150,7 @@ class DAUConvOpB200 : public DAUOpBase {
         const Tensor &input = ctx->input(0), &w = ctx->input(1), &mu1 = ctx->input(2), &mu2 = ctx->input(3),
                      &sigma = ctx->input(4);
         size_t fwd = 0, bwd = 0;
+        std::lock_guard<std::mutex> lock(mu_);          // held across planning, the launch and the flag read
         OP_REQUIRES_OK(ctx, Prepare(ctx, input, w, mu1, mu2, sigma, &fwd, &bwd));
         Tensor* out = nullptr;
         OP_REQUIRES_OK(ctx, ctx->allocate_output(0, TensorShape({input.dim_size(0), st_.num_output, input.dim_size(2),
@@ -170,6 +172,7 @@ class DAUConvGradOpB200 : public DAUOpBase {
         const Tensor &grad = ctx->input(0), &input = ctx->input(1), &w = ctx->input(2), &mu1 = ctx->input(3),
                      &mu2 = ctx->input(4), &sigma = ctx->input(5);
         size_t fwd = 0, bwd = 0;
+        std::lock_guard<std::mutex> lock(mu_);          // held across planning, the launch and the flag read
         OP_REQUIRES_OK(ctx, Prepare(ctx, input, w, mu1, mu2, sigma, &fwd, &bwd));
         Tensor *gi = nullptr, *gw = nullptr, *gm1 = nullptr, *gm2 = nullptr, *gs = nullptr;
         OP_REQUIRES_OK(ctx, ctx->allocate_output(0, input.shape(), &gi));
