@@ -22,3 +22,5 @@ python tests/ref_cuda_time.py --config c4 --images 64 >> gpurun_out/${T}_referen
 fi
 python -m pytest tests -m gpu -q > gpurun_out/${T}_pytest_gpu_final.log 2>&1; tail -3 gpurun_out/${T}_pytest_gpu_final.log
 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/${T}_smoke.log 2>&1; tail -1 gpurun_out/${T}_smoke.log
+python tools/alexnet_breakdown.py --batch 32 --rows 45 > gpurun_out/${T}_alexnet_breakdown_b32.txt 2>&1
+python tools/alexnet_breakdown.py --batch 256 --rows 45 > gpurun_out/${T}_alexnet_breakdown_b256.txt 2>&1
