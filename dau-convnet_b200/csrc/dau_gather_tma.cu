@@ -278,36 +278,76 @@ dau_gather_tma_kernel(const __grid_constant__ CUtensorMap in_map, const TGatherP
     store_strip<R>(p, acc, np, co, lx, ly, x0, y0, s_rowmap, s_colmap);
 }
 
-// Sums the split_k partial strips of one tail item in part order and stores them like any other.
+// One row (r) of a lane's strip, both images: the epilogue of store_strip for the kernel that sums split items.
 template <int R>
-__global__ void __launch_bounds__(NW * 32) gather_tail_kernel(const TGatherParams p) {
+__device__ __forceinline__ void store_row(const TGatherParams& p, const float2 (&acc)[C], int np, int co, int lx, int ly,
+                                          int r, int x0, int y0, const int* s_rowmap, const int* s_colmap) {
+    const float bv = p.bias ? __ldg(p.bias + co) : 0.f;
+    const int xs = x0 + lx * C;
+    const int H = p.H, W = p.W;
+    const bool ident = p.m.kx == 1 && p.m.ky == 1;
+    const int crop = p.crop, RH = p.m.H - 2 * crop, RW = p.m.W - 2 * crop;
+    const bool vec = ident && crop == 0 && ((W & 3) == 0) && (xs + C <= W);
+    const size_t rplane = (size_t)RH * RW;
+    const int y = y0 + ly * p.ly_stride + r;
+    if (y >= H) return;
+#pragma unroll
+    for (int img = 0; img < 2; ++img) {
+        const int n = 2 * np + img;
+        if (n >= p.N) break;
+        float v[C];
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+            v[c] = (img == 0 ? acc[c].x : acc[c].y) + bv;
+            if (p.relu) v[c] = fmaxf(v[c], 0.f);
+        }
+        if (vec) {
+            float* orow = p.out + ((size_t)n * p.Cout + co) * rplane + (size_t)y * W;
+            *reinterpret_cast<float4*>(orow + xs) = make_float4(v[0], v[1], v[2], v[3]);
+        } else {
+            const int rm = s_rowmap[ly * R + r];
+#pragma unroll
+            for (int c = 0; c < C; ++c) {
+                const int cm = s_colmap[lx * C + c];
+                const int rn = (n * p.m.ky + (rm >> 16)) * p.m.kx + (cm >> 16);
+                const int ry = (rm & 0xffff) - crop, rx = (cm & 0xffff) - crop;
+                if ((rm | cm) >= 0 && rn < p.m.N && (unsigned)ry < (unsigned)RH && (unsigned)rx < (unsigned)RW)
+                    p.out[((size_t)rn * p.Cout + co) * rplane + (size_t)ry * RW + rx] = v[c];
+            }
+        }
+    }
+}
+
+// Sums the split_k partial strips of one tail item in part order (deterministic) and stores them like any other.
+// grid = (tail items, output channels of the group), block = R warps: thread (lane, r) owns row r of lane's strip, so
+// the serial work of a thread is split_k x 4 coalesced loads -- on the latency-bound shapes (BASELINE config C1, the
+// reference's speed-test shape) the first version of this kernel, one thread per whole strip, took longer than the
+// gather it finishes (39 us against 15 us on C1).
+template <int R>
+__global__ void __launch_bounds__(32 * R) gather_tail_kernel(const TGatherParams p) {
     constexpr int TH = LY * R;
     const int item = p.full_items + blockIdx.x;
     const int tile_i = item % p.gx, cg = (item / p.gx) % p.gy, np = item / (p.gx * p.gy);
     const int tyi = tile_i / p.tiles_x, txi = tile_i - tyi * p.tiles_x;
     const int x0 = txi * TW, y0 = tyi * p.tile_pitch_y;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x, lane = tid & 31, r = tid >> 5, warp = blockIdx.y;
     __shared__ int s_rowmap[TH], s_colmap[TW];
     build_store_maps<TH>(p, x0, y0, tid, s_rowmap, s_colmap);
     __syncthreads();
     const int co = cg * NW + warp;
     if (co >= p.Cout) return;
-    float2 acc[R][C];
+    float2 acc[C];
 #pragma unroll
-    for (int r = 0; r < R; ++r)
-#pragma unroll
-        for (int c = 0; c < C; ++c) acc[r][c] = make_float2(0.f, 0.f);
+    for (int c = 0; c < C; ++c) acc[c] = make_float2(0.f, 0.f);
     for (int part = 0; part < p.split_k; ++part) {
         const float2* src = p.part + ((size_t)(blockIdx.x * p.split_k + part) * NW + warp) * (R * C * 32) + lane;
 #pragma unroll
-        for (int r = 0; r < R; ++r)
-#pragma unroll
-            for (int c = 0; c < C; ++c) {
-                const float2 v = src[(r * C + c) * 32];
-                acc[r][c].x += v.x; acc[r][c].y += v.y;
-            }
+        for (int c = 0; c < C; ++c) {
+            const float2 v = src[(r * C + c) * 32];
+            acc[c].x += v.x; acc[c].y += v.y;
+        }
     }
-    store_strip<R>(p, acc, np, co, lane & (LX - 1), lane >> 4, x0, y0, s_rowmap, s_colmap);
+    store_row<R>(p, acc, np, co, lane & (LX - 1), lane >> 4, r, x0, y0, s_rowmap, s_colmap);
 }
 
 constexpr int kHalos[4] = {4, 8, 16, 32};
@@ -324,7 +364,7 @@ void launch_t(const GatherPlan& plan, const CUtensorMap& map, const TGatherParam
     const long long ctas = plan.full_items + (items - plan.full_items) * plan.split_k;
     dau_gather_tma_kernel<HALO, R><<<(unsigned)ctas, NTHREADS, plan.smem_bytes, stream>>>(map, p);
     if (plan.full_items < items)
-        gather_tail_kernel<R><<<(unsigned)(items - plan.full_items), NW * 32, 0, stream>>>(p);
+        gather_tail_kernel<R><<<dim3((unsigned)(items - plan.full_items), NW), 32 * R, 0, stream>>>(p);
 }
 
 template <int HALO, int R>
