@@ -248,6 +248,23 @@ dau_status_t dau_plan_mosaic(int N, int H, int W, int gap, int* out10) {
     });
 }
 
+dau_status_t dau_plan_strips(int N, int H, int W, int gap, long long* counts2, int* items_out, long long capacity) {
+    if (!counts2) return fail(DAU_ERR_INVALID_ARGUMENT, "dau_plan_strips: NULL output");
+    return guarded([&] {
+        DAU_CHECK(N > 0 && H > 0 && W > 0 && gap >= 0, 1, "dau_plan_strips: sizes must be positive");
+        const dau::Mosaic m = dau::plan_mosaic(N, H, W, gap);
+        const dau::StripGeom g = dau::strip_geometry(m, 1);
+        counts2[0] = g.full_items; counts2[1] = g.tail_items;
+        if (!items_out) return;
+        DAU_CHECK(capacity >= g.full_items + g.tail_items, 1, "dau_plan_strips: items_out too small");
+        long long k = 0;
+        for (int tail = 0; tail < 2; ++tail)
+            for (long long i = 0; i < (tail ? g.tail_items : g.full_items); ++i, ++k)
+                dau::strip_item_origin(m, i, tail != 0, &items_out[4 * k], &items_out[4 * k + 1], &items_out[4 * k + 2],
+                                       &items_out[4 * k + 3]);
+    });
+}
+
 int dau_mosaic_to_real(const int* q, int N, int nv, int vy, int vx, int* n, int* y, int* x) {
     if (!q || !n || !y || !x) return 0;
     dau::Mosaic m;

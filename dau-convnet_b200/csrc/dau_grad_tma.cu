@@ -111,7 +111,7 @@ struct TGradParams {
 };
 
 // (pair, first mosaic row, column tile) of a full (tail == false) or tail item
-__device__ __forceinline__ void item_origin(const TGradParams& p, long long item, bool tail, int* np, int* y0, int* txi) {
+__host__ __device__ __forceinline__ void item_origin(const TGradParams& p, long long item, bool tail, int* np, int* y0, int* txi) {
     const int tx = (int)(item % p.tiles_x);
     long long v = item / p.tiles_x;
     int t = p.q;
@@ -373,6 +373,16 @@ StripGeom strip_geometry(const Mosaic& m, int S) {
     g.total_floats = g.tail_base_floats + (size_t)g.tail_items * S * (g.tail * 4 * XK_ROW_BYTES / 4);
     return g;
 }
+// Host view of the kernel's own item -> (image pair, first mosaic row, rows, column tile) map (test hook)
+void strip_item_origin(const Mosaic& m, long long item, bool tail, int* pair, int* y0, int* rows, int* tile_x) {
+    const StripGeom g = strip_geometry(m, 1);
+    TGradParams p;
+    memset(&p, 0, sizeof(p));
+    p.tiles_x = g.tiles_x; p.ky = g.ky; p.py = g.py; p.q = g.q;
+    item_origin(p, item, tail, pair, y0, tile_x);
+    *rows = tail ? g.tail : R;
+}
+
 size_t error_layout_floats(int N, int F, int H, int W) {
     const size_t qv = (W + 1) / 2, qp = (qv + 1) / 2 * 2;
     return (size_t)((N + 1) / 2) * F * H * 2 * qp * 2;

@@ -145,6 +145,7 @@ struct StripGeom {
     size_t total_floats;
 };
 StripGeom strip_geometry(const Mosaic& m, int S);
+void strip_item_origin(const Mosaic& m, long long item, bool tail, int* pair, int* y0, int* rows, int* tile_x);
 
 // TMA variant: Xk in the strip-major layout XS (launch_blur_bank_strips), the error in the de-interleaved
 // pair layout SGP[n/2][f][y][x%2][x/2][n%2] with the edge mask applied (launch_error_relayout)

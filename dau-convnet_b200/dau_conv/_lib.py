@@ -14,7 +14,7 @@ SYMBOLS = [
     "dau_last_error", "dau_abi_version", "dau_settings_default", "dau_create", "dau_destroy",
     "dau_reshape", "dau_get_output_size", "dau_set_sigma_hint", "dau_set_offset_hint", "dau_forward", "dau_backward", "dau_set_activation", "dau_backward_act", "dau_take_nan_flag",
     "dau_get_kernels",
-    "dau_forward_host", "dau_backward_host", "dau_train_step_host", "dau_plan_mosaic", "dau_mosaic_to_real", "dau_bias_grad_static", "dau_edge_mask_rule", "dau_debug_unit_tables", "dau_measure_fma_peak", "dau_enable_timing",
+    "dau_forward_host", "dau_backward_host", "dau_train_step_host", "dau_plan_mosaic", "dau_plan_strips", "dau_mosaic_to_real", "dau_bias_grad_static", "dau_edge_mask_rule", "dau_debug_unit_tables", "dau_measure_fma_peak", "dau_enable_timing",
     "dau_get_timing", "dau_timing_name", "dau_launch_count",
 ]
 
@@ -69,6 +69,7 @@ lib.dau_forward_host.argtypes = [_vp, C.c_int, C.c_int, C.c_int, C.c_int] + [_vp
 lib.dau_backward_host.argtypes = [_vp, C.c_int, C.c_int, C.c_int, C.c_int] + [_vp] * 13 + [C.c_uint]
 lib.dau_train_step_host.argtypes = [_vp] + [C.c_int] * 5 + [C.c_float] + [_vp] * 12 + [_vp]
 lib.dau_plan_mosaic.argtypes = [C.c_int] * 4 + [C.POINTER(C.c_int)]
+lib.dau_plan_strips.argtypes = [C.c_int] * 4 + [C.POINTER(C.c_longlong), C.POINTER(C.c_int), C.c_longlong]
 lib.dau_mosaic_to_real.argtypes = [C.POINTER(C.c_int), C.c_int, C.c_int, C.c_int, C.c_int] + [C.POINTER(C.c_int)] * 3
 lib.dau_mosaic_to_real.restype = C.c_int
 lib.dau_bias_grad_static.argtypes = [C.c_int, _vp, _vp, _vp, C.c_int, C.c_int, C.c_int, C.c_int, _vp]

@@ -193,6 +193,11 @@ dau_status_t dau_train_step_host(dau_handle_t* h, int N, int S, int H, int W, in
  * dau_mosaic_to_real: mosaic pixel (nv, vy, vx) -> real pixel; returns 1 and fills n/y/x for
  * image pixels, 0 for gap pixels and for cells beyond the batch. */
 dau_status_t dau_plan_mosaic(int N, int H, int W, int gap, int* out10);
+/* dau_plan_strips: the work items of the parameter-gradient kernel for that mosaic -- row strips of 4 rows and one
+ * tail strip of H % 4 rows per cell row, never a gap row (reference: the 8-row warp tiles of its patches,
+ * dau_conv_backward_core.hpp:1017-1100, have no counterpart of this).  counts2 = {full items, tail items};
+ * items_out (may be NULL) receives {image pair, first mosaic row, rows, 64-column tile} per item, full items first. */
+dau_status_t dau_plan_strips(int N, int H, int W, int gap, long long* counts2, int* items_out, long long capacity);
 int dau_mosaic_to_real(const int* mosaic10, int N, int nv, int vy, int vx, int* n, int* y, int* x);
 
 /* Allocation-free bias gradient.  NO COUNTERPART IN THE REFERENCE: added

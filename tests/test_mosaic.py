@@ -69,3 +69,35 @@ def test_out_of_range_queries_and_bad_sizes():
     out = (C.c_int * 10)()
     assert _lib.lib.dau_plan_mosaic(0, 13, 13, 4, out) != 0
     assert b"positive" in _lib.lib.dau_last_error()
+
+
+@pytest.mark.parametrize("N,H,W,gap", [(256, 13, 13, 4), (32, 13, 13, 4), (256, 27, 27, 4), (256, 28, 28, 8), (7, 27, 27, 4),
+                                       (9, 13, 11, 6), (33, 6, 5, 4), (1, 8, 8, 4), (128, 64, 64, 4), (3, 65, 8, 4),
+                                       (5, 3, 70, 4), (4, 1, 1, 4), (16, 16, 16, 4), (2, 130, 129, 16)])
+def test_gradient_row_strips_cover_every_real_row_once_and_no_gap_row(N, H, W, gap):
+    """dau_plan_strips (the gradient kernel's own item -> origin map, StripGeom in dau_kernels.cuh): H // 4 full strips
+    of 4 rows + one tail strip of H % 4 rows per cell row; gap rows belong to no strip; the 64-column tiles cover the
+    mosaic width; items are numbered the way the strip-major Xk layout is written (full items first)."""
+    q, m = plan(N, H, W, gap)
+    counts = (C.c_longlong * 2)()
+    _lib.check(_lib.lib.dau_plan_strips(N, H, W, gap, counts, None, 0))
+    n_full, n_tail = counts[0], counts[1]
+    pairs, tiles_x = -(-m["Nv"] // 2), -(-m["Wv"] // 64)
+    assert n_full == pairs * m["ky"] * (H // 4) * tiles_x
+    assert n_tail == (pairs * m["ky"] * tiles_x if H % 4 else 0)
+    items = (C.c_int * (4 * (n_full + n_tail)))()
+    _lib.check(_lib.lib.dau_plan_strips(N, H, W, gap, counts, items, n_full + n_tail))
+    it = np.array(list(items), np.int64).reshape(-1, 4)
+    cover = np.zeros((pairs, m["Hv"], tiles_x), np.int32)
+    for k, (pair, y0, rows, tx) in enumerate(it):
+        assert 0 <= pair < pairs and 0 <= tx < tiles_x and y0 >= 0 and y0 + rows <= m["Hv"]
+        assert rows == (4 if k < n_full else H % 4) and rows > 0
+        cover[pair, y0:y0 + rows, tx] += 1
+    real_row = np.array([(vy % m["py"]) < H for vy in range(m["Hv"])])
+    assert (cover[:, real_row, :] == 1).all()               # every real row of every cell row, once per column tile
+    assert (cover[:, ~real_row, :] == 0).all()               # gap rows are nobody's work
+    # a strip never crosses a cell row
+    for pair, y0, rows, tx in it:
+        assert y0 // m["py"] == (y0 + rows - 1) // m["py"]
+    with pytest.raises(_lib.DAUError):
+        _lib.check(_lib.lib.dau_plan_strips(N, H, W, gap, counts, items, 0 if n_full + n_tail else -1))
