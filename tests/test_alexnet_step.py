@@ -68,6 +68,17 @@ def test_graph_replay_equals_eager():
     assert _rel(b.body.p, a.body.p) < 1e-4 and _rel(b.head.p, a.head.p) < 1e-4
 
 
+def test_overlapped_head_update_equals_the_plain_step():
+    """overlap_sgd: the FC head's SGD on a side stream under the body's backward pass -- same parameters after 4 steps."""
+    import torch
+    a = _trainer(global_batch=4, device="cuda:0", overlap_sgd=False)
+    b = _trainer(global_batch=4, device="cuda:0", overlap_sgd=True)
+    for _ in range(4):
+        a.step(); b.step()
+    torch.cuda.synchronize()
+    assert torch.equal(a.head.p, b.head.p) and _rel(b.body.p, a.body.p) < 1e-5
+
+
 def _free_port():
     s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close(); return p
 

@@ -69,6 +69,10 @@ SHAPES = [
     # narrow maps packed into mosaics (several images per 64-px tile, cells beyond the batch)
     (16, 13, 13, 8, 8, (1, 2), 9, 3.9), (9, 13, 13, 3, 5, (1, 2), 9, 3.9), (12, 27, 27, 4, 6, (1, 2), 9, 3.9),
     (8, 28, 28, 4, 4, (1, 2), 17, 8), (33, 6, 5, 2, 3, (2, 2), 9, 3.9),
+    # the gathers' cell-row mode (cells of 13..16 rows stacked in the mosaic: strip height = image height) at every such
+    # height, with several 64-column tiles and an odd batch; the gradient kernel's tail strips of 1, 2 and 3 rows
+    (20, 40, 14, 3, 4, (1, 2), 9, 3.9), (30, 64, 15, 2, 3, (1, 2), 9, 3.9), (40, 16, 16, 4, 5, (1, 2), 9, 3.9),
+    (23, 50, 13, 2, 9, (2, 1), 9, 3.9),
 ]
 
 
