@@ -42,11 +42,15 @@ def _static_entry_point(dev, err, y_act, F):
     import torch
     from dau_conv import _lib
     N, _, H, W = err.shape
+    import gc
     dbias = torch.full((F,), 0.25, device=dev)
-    before = torch.cuda.memory_allocated(dev)
+    gc.collect()
+    # torch's allocator counts every allocation it serves (monotonic; frees by a late garbage collection of other
+    # tests' tensors do not touch it): the call must not add one
+    before = torch.cuda.memory_stats(dev)["allocation.all.allocated"]
     _lib.check(_lib.lib.dau_bias_grad_static(dev.index, err.data_ptr(), y_act.data_ptr() if y_act is not None else None,
                                              dbias.data_ptr(), N, F, H, W, torch.cuda.current_stream(dev).cuda_stream))
-    assert torch.cuda.memory_allocated(dev) == before            # nothing went through torch's allocator either
+    assert torch.cuda.memory_stats(dev)["allocation.all.allocated"] == before
     torch.cuda.synchronize(dev)
     return dbias.cpu().numpy()
 
